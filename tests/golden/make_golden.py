@@ -1,0 +1,108 @@
+"""Regenerates tests/golden/runs.json + *.npz.  Run in the build container (needs /root/reference
+compiled into oracle/_ref by oracle/Makefile):   python tests/golden/make_golden.py
+
+ * serial-order cases: the time loop of reference src/serial/main.c:86-147 is driven from here
+   with the UNMODIFIED reference functions (libnsref.so: max_mat, set_noslip/set_inflow, FG, SOR,
+   dp_dx, dp_dy); only the two inline loops of main.c (RHS :116-120, update :131-136) are numpy /
+   python restatements.  The oracle must reproduce these bit for bit.
+ * red-black cases: the reference's CUDA build cannot run in the container (no GPU), so these are
+   written by the oracle AFTER it has passed every serial-order check; they pin the oracle against
+   silent drift and give the GPU tests a committed target.
+"""
+import ctypes as C
+import json
+import math
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from oracle import binding as ob  # noqa: E402
+
+GOLD = os.path.dirname(os.path.abspath(__file__))
+
+
+def run_reference_serial(P):
+    R = ob.ref()
+    ni, nj = P.i_max, P.j_max
+    u, v, p, F, G, RHS, res = (ob.zeros(P) for _ in range(7))
+    ur, vr, pr, Fr, Gr, RHSr, resr = (ob.rows(x) for x in (u, v, p, F, G, RHS, res))
+    dx, dy = P.a / ni, P.b / nj
+    t, log = 0.0, []
+    while t < P.T:
+        umax = R.max_mat(ni, nj, ur)
+        vmax = R.max_mat(ni, nj, vr)
+        with np.errstate(divide="ignore"):
+            cands = [P.Re / 2.0 / (1.0 / dx / dx + 1.0 / dy / dy),
+                     float(np.float64(dx) / np.float64(abs(umax))),
+                     float(np.float64(dy) / np.float64(abs(vmax)))]
+        m = cands[0]
+        for c in cands[1:]:
+            if m > c:
+                m = c
+        dt = P.tau * m
+        gamma = max(umax * dt / dx, vmax * dt / dy)
+        lid = 1.0 if P.problem == 1 else math.sin(P.f * t)
+        R.set_noslip(ni, nj, ur, vr, ob.LEFT)
+        R.set_noslip(ni, nj, ur, vr, ob.RIGHT)
+        R.set_noslip(ni, nj, ur, vr, ob.BOTTOM)
+        R.set_inflow(ni, nj, ur, vr, ob.TOP, lid, 0.0)
+        R.FG(Fr, Gr, ur, vr, ni, nj, P.Re, P.g_x, P.g_y, dt, dx, dy, gamma)
+        RHS[1:-1, 1:-1] = 1.0 / dt * ((F[1:-1, 1:-1] - F[:-2, 1:-1]) / dx + (G[1:-1, 1:-1] - G[1:-1, :-2]) / dy)
+        ret = R.SOR(pr, ni, nj, dx, dy, resr, RHSr, P.omega, P.epsilon, P.max_it)
+        for i in range(1, ni + 1):
+            for j in range(1, nj + 1):
+                if i <= ni - 1:
+                    u[i, j] = F[i, j] - dt * R.dp_dx(pr, i, j, dx)
+                if j <= nj - 1:
+                    v[i, j] = G[i, j] - dt * R.dp_dy(pr, i, j, dy)
+        log.append(dict(dt=dt, ret=ret))
+        t += dt
+    return dict(u=u, v=v, p=p, log=log)
+
+
+CASES = [
+    dict(name="serial_32", sor_order=0, params=dict(i_max=32, j_max=32, T=1.5)),
+    dict(name="serial_24x40_osc", sor_order=0, params=dict(i_max=24, j_max=40, T=1.2, problem=2, f=3.0, b=1.5)),
+    dict(name="rb_32", sor_order=1, params=dict(i_max=32, j_max=32, T=1.5)),
+    dict(name="rb_24x40_osc", sor_order=1, params=dict(i_max=24, j_max=40, T=1.2, problem=2, f=3.0, b=1.5)),
+    dict(name="rb_33x31", sor_order=1, params=dict(i_max=33, j_max=31, T=0.1, a=1.1, b=0.9, Re=100.0, max_it=300)),
+    dict(name="rb_64", sor_order=1, params=dict(i_max=64, j_max=64, T=0.1)),
+]
+
+
+def main():
+    out = []
+    for c in CASES:
+        P = ob.make_params(**c["params"])
+        got = ob.run(P, sor_order=c["sor_order"])
+        if c["sor_order"] == 0:
+            ref = run_reference_serial(P)
+            for k in ("u", "v", "p"):
+                assert np.array_equal(ref[k], got[k]), (c["name"], k)
+            assert [s["dt"] for s in ref["log"]] == [s["dt"] for s in got["log"]]
+            fields = ref
+            src = "reference functions (oracle/_ref/libnsref.so)"
+        else:
+            fields = got
+            src = "oracle red-black restatement of src/parallel/main.cu:656-726"
+        fn = c["name"] + ".npz"
+        np.savez_compressed(os.path.join(GOLD, fn), u=fields["u"], v=fields["v"], p=fields["p"])
+        ic, jc = P.i_max // 2, P.j_max // 2
+        out.append(dict(name=c["name"], source=src, sor_order=c["sor_order"], params=c["params"],
+                        steps=got["steps"], sor_iters=[s["sor_iters"] for s in got["log"]],
+                        sor_ret=[s["sor_ret"] for s in got["log"]],
+                        dt_hex=[s["dt"].hex() for s in got["log"]],
+                        norm_p_hex=[s["norm_p"].hex() for s in got["log"]],
+                        res_hex=[s["res"].hex() for s in got["log"]],
+                        u_center_hex=float(fields["u"][ic, jc]).hex(),
+                        v_center_hex=float(fields["v"][ic, jc]).hex(), fields=fn))
+        print(c["name"], got["steps"], "steps, iters", [s["sor_iters"] for s in got["log"]][:6])
+    with open(os.path.join(GOLD, "runs.json"), "w") as fh:
+        json.dump(out, fh, indent=1)
+
+
+if __name__ == "__main__":
+    main()
