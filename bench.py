@@ -1,0 +1,298 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark: SOR MLUPS (and time steps/s) of the lid-driven-cavity time step.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--size 8192]
+
+Workload (BASELINE.json configs[2], the one the metric is quoted on; SURVEY 8d "C3"): synthetic
+lid-driven cavity, 8192 x 8192 cells, FP64, Re=1000, a=b=1, tau=1, omega=1.7, eps=1e-4, max_it=500.
+Deterministic: all fields start at zero, lid u=1 -- no RNG.  One "step" = one whole time step
+(dt reduction, boundary conditions, F/G, RHS, red-black SOR with the residual test every iteration
+-- 500 iterations, it cannot converge at this size -- velocity update).  1 LUP = one interior cell
+receiving its red-or-black update once; MLUPS counts SOR iterations actually performed x cells.
+
+Timed region: K steps bracketed by barrier + synchronize, CUDA events on the stream the kernels
+are launched on, max over ranks.  L2: one pressure grid is 537 MB >> 126 MB L2, every iteration
+streams 1.6 GB, so inputs are larger than L2 (no flush needed; stated in config.l2).
+
+Also reported: e2e (same steps through the host-grid call nsb_timestep with HOST buffers, pinned,
+H2D/D2H inside the timed region), roofline of the dominant kernel (sor_stream_kernel, 24 B per
+LUP against the measured HBM copy bandwidth), cpu_baseline (the unmodified reference serial SOR,
+oracle/_ref, 1 core, bounded sample).  --impl reference times only that CPU reference.
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+
+def pkg():
+    return importlib.import_module("navierstokes-parallel_b200")
+
+
+def workload_params(m_or_ob, size, max_it):
+    return m_or_ob.make_params(problem=1, f=1.0, i_max=size, j_max=size, a=1.0, b=1.0, T=1.0e9, Re=1000.0,
+                               g_x=0.0, g_y=0.0, tau=1.0, omega=1.7, epsilon=1e-4, max_it=max_it, n_print=1)
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thr = threading.Thread(target=self._pump, daemon=True)
+            self.thr.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, smax, reasons, pw = [], None, set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, line in self.rows:
+            if ts < t0 - 0.05 or ts > t1 + 0.05:
+                continue
+            f = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(f[0])); smax = float(f[1]); pw.append(float(f[2]))
+            except Exception:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------- CPU reference leg
+def cpu_reference_sor(size, iters_per_step, steps, warmup):
+    """Times the reference's own serial SOR (src/serial/integration.c:129-173, compiled unmodified
+    into oracle/_ref/libnsref.so; falls back to the oracle port if that build is absent) on the
+    bench workload: p = 0, RHS = the cavity's first-step RHS, `iters_per_step` sweeps per step."""
+    from oracle import binding as ob
+    P = workload_params(ob, size, iters_per_step)
+    L = ob.lib()
+    ni = nj = size
+    dx, dy = P.a / ni, P.b / nj
+    u, v, F, G, RHS, p, res = (ob.zeros(P) for _ in range(7))
+    dt, gamma = C.c_double(), C.c_double()
+    L.orc_dt_gamma(C.byref(P), dx, dy, 0.0, 0.0, C.byref(dt), C.byref(gamma))
+    L.orc_apply_bc(C.byref(P), 0.0, ob._ptr(u), ob._ptr(v))
+    L.orc_FG(ob._ptr(F), ob._ptr(G), ob._ptr(u), ob._ptr(v), ni, nj, P.Re, 0.0, 0.0, dt.value, dx, dy, gamma.value)
+    L.orc_RHS(ob._ptr(RHS), ob._ptr(F), ob._ptr(G), ni, nj, dt.value, dx, dy)
+    kind = "reference" if ob.have_ref() else "port"
+    if kind == "reference":
+        R = ob.ref()
+        pr, rr, hr = ob.rows(p), ob.rows(res), ob.rows(RHS)
+        run = lambda: R.SOR(pr, ni, nj, dx, dy, rr, hr, P.omega, 0.0, iters_per_step)   # eps=0: no early exit
+    else:
+        run = lambda: ob.sor_lex(p, RHS, dx, dy, P.omega, 0.0, iters_per_step)
+    for _ in range(warmup):
+        run()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        run()
+    el = time.perf_counter() - t0
+    lups = float(steps) * iters_per_step * ni * nj
+    return {"value": lups / el / 1e6, "unit": "MLUPS", "cores": 1, "kind": kind,
+            "sample": f"{steps} x SOR({iters_per_step} lexicographic sweeps, residual every sweep) on the "
+                      f"{size}x{size} cavity RHS, {'oracle/_ref/libnsref.so (unmodified reference serial SOR)' if kind == 'reference' else 'oracle port'}, "
+                      f"single thread (the reference is single-threaded), {el:.1f} s",
+            "seconds": el, "ms_per_step": el / steps * 1e3}
+
+
+# ----------------------------------------------------------------------------- main
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--size", type=int, default=8192)
+    ap.add_argument("--max-it", type=int, default=500)
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--engine", type=int, default=0)
+    ap.add_argument("--chunk-rows", type=int, default=0)
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    size, max_it = args.size, args.max_it
+    cells = float(size) * float(size)
+    workload = (f"synthetic lid-driven cavity {size}x{size} FP64, Re=1000, omega=1.7, eps=1e-4, "
+                f"max_it={max_it} (BASELINE.json configs[2])")
+    config = {"workload": workload, "grid": [size, size], "max_it": max_it, "parallelism": f"y-slabs x{world}" if world > 1 else "single GPU",
+              "l2": "inputs larger than L2 (537 MB per grid at 8192^2 vs 126 MB L2); no flush"}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        # bounded sample: 1 lexicographic sweep over the 8192^2 grid ~ 1.1 s on one core
+        ips = 2 if size >= 4096 else max(2, int(2e8 / cells))
+        b = cpu_reference_sor(size, ips, max(1, args.steps), max(1, min(args.warmup, 1)))
+        line = {"impl": "reference", "metric": "sor_mlups", "value": b["value"], "unit": "MLUPS", "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": b["ms_per_step"], "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+                "cpu_baseline": {k: b[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "e2e": {"value": b["value"], "unit": "MLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    m = pkg()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    P = workload_params(m, size, max_it)
+    s = m.Solver(P, device=local, sor_engine=args.engine, chunk_rows=args.chunk_rows)
+    stream = torch.cuda.ExternalStream(s.stream, device=torch.device("cuda", local))
+
+    # ---- device-resident steps
+    t = 0.0
+    for _ in range(args.warmup):
+        info = s.step(t); t += info["dt"]
+    sampler = ClockSampler(local)
+    sampler.start()
+    time.sleep(0.3)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    w0 = time.time()
+    e0.record(stream)
+    iters = 0
+    for _ in range(args.steps):
+        info = s.step(t); t += info["dt"]; iters += info["sor_iters"]
+    e1.record(stream)
+    barrier()
+    w1 = time.time()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop(w0, w1)
+    if world > 1:
+        tt = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms = float(tt.item())
+    total_lups = float(iters) * cells * world          # replicas / slabs: every rank did `iters` sweeps of its cells
+    value = total_lups / (ms * 1e-3) / 1e6
+    launches = args.steps * (4 + 2 + 1 + (iters // max(1, args.steps)) + 1 + 1)
+
+    # ---- dominant kernel alone: average launch duration over a fixed batch of iterations
+    barrier()
+    n_k = 100
+    s.sor_iterations(10)
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k0.record(stream)
+    s.sor_iterations(n_k)
+    k1.record(stream)
+    torch.cuda.synchronize()
+    k_ms = k0.elapsed_time(k1) / n_k
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = 24.0 * cells / (k_ms * 1e-3) / 1e9
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "sor_stream_traffic.json"))).get("dram_bytes_per_launch")
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "kernel": "sor_stream_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
+                "algorithmic_bytes_per_launch": 24.0 * cells, "launch_ms": k_ms,
+                "kernel_mlups": cells / (k_ms * 1e-3) / 1e6}
+
+    # ---- end to end: host grids in, host grids out (nsb_timestep), pinned host memory
+    e2e = None
+    if not args.no_e2e:
+        L = m.lib()
+        ni = nj = size
+        hu = torch.zeros((ni + 1, nj + 2), dtype=torch.float64).pin_memory()
+        hv = torch.zeros((ni + 2, nj + 1), dtype=torch.float64).pin_memory()
+        hp = torch.zeros((ni + 2, nj + 2), dtype=torch.float64).pin_memory()
+        ur, vr, pr = m.rows(hu.numpy()), m.rows(hv.numpy()), m.rows(hp.numpy())
+        null = C.cast(None, m.dbl_pp)
+        info = m.StepInfo()
+        tt_, it2 = 0.0, 0
+        rc = L.nsb_timestep(C.byref(P), tt_, ur, vr, pr, null, null, null, C.byref(info))     # warm-up (allocates)
+        assert rc == 0, rc
+        tt_ += info.dt
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            rc = L.nsb_timestep(C.byref(P), tt_, ur, vr, pr, null, null, null, C.byref(info))
+            assert rc == 0, rc
+            tt_ += info.dt; it2 += info.sor_iters
+        barrier()
+        el = time.perf_counter() - t0
+        if world > 1:
+            t2 = torch.tensor([el], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+            el = float(t2.item())
+        bi = (hu.numel() + hv.numel() + hp.numel()) * 8
+        e2e = {"value": float(it2) * cells * world / el / 1e6, "unit": "MLUPS", "h2d_bytes_per_step": bi,
+               "d2h_bytes_per_step": bi, "steps": args.e2e_steps, "ms_per_step": el / args.e2e_steps * 1e3,
+               "api": "nsb_timestep(double** u, v, p) -- upload, whole step in HBM, download"}
+        L.nsb_host_api_reset()
+    s.close()
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        b = cpu_reference_sor(size, 2 if size >= 4096 else max(2, int(2e8 / cells)), 8 if size >= 4096 else 5, 1)
+        cpu = {k: b[k] for k in ("value", "unit", "cores", "kind", "sample")}
+
+    if rank == 0:
+        line = {"metric": "sor_mlups", "value": value, "unit": "MLUPS", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+                "timesteps_per_s": args.steps / (ms * 1e-3), "sor_iters_per_step": iters / max(1, args.steps),
+                "hbm_gbs_whole_step": (80.0 + 24.0 * iters / max(1, args.steps)) * cells * world * args.steps / (ms * 1e-3) / 1e9,
+                "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

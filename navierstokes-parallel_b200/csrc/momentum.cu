@@ -1,0 +1,303 @@
+// momentum.cu -- everything of the time step that is not the pressure solve:
+//   boundary conditions (boundaries.c:7-39 ; set_*_kernel main.cu:838-925),
+//   F and G (integration.c:7-96 ; calculate_F/G_kernel main.cu:289-382),
+//   Poisson right-hand side (main.c:116-120 ; calculate_RHS_kernel main.cu:219-229),
+//   velocity update (main.c:131-136 ; update_velocities_kernel main.cu:231-245) fused with the
+//   reductions the NEXT step needs: signed max u, max v (io.c:122-139 ; find_max_kernel
+//   main.cu:729-796) and sum p^2 (integration.c:115-124 ; calculate_norm_kernel main.cu:593-622).
+//
+// All kernels run x-fastest over the pitched grids, one thread per cell, threadIdx.x along i:
+// a warp touches 256 contiguous bytes per array (the reference maps threadIdx.x to the strided
+// index).  Arithmetic order is the reference's, evaluated with non-contracting
+// intrinsics (nsb_math.cuh), so F, G, RHS, u, v are bit-identical to the CPU build.
+#include "nsb_internal.h"
+#include "nsb_math.cuh"
+
+#define MB_X 128
+#define MB_Y 2
+
+struct MomCoef {
+    double dt, gamma;
+    double inv_dx, inv_dy;       // 1/delta_x, 1/delta_y            integration.c:14,26
+    double g_dx, g_dy;           // gamma/delta_x, gamma/delta_y
+    double dx2, dy2, rdx2, rdy2; // delta_x*delta_x ...              integration.c:58
+    double dx, dy, rdx, rdy;
+    double inv_re;               // 1.0/Re                          integration.c:79
+    double inv_dt;               // 1.0/delta_t                     main.c:118
+    double g_x, g_y;
+};
+
+static MomCoef make_mom(const nsb_ctx* c, double dt, double gamma) {
+    MomCoef m;
+    m.dt = dt; m.gamma = gamma;
+    m.dx = c->dx; m.dy = c->dy;
+    m.inv_dx = 1 / c->dx; m.inv_dy = 1 / c->dy;
+    m.g_dx = gamma / c->dx; m.g_dy = gamma / c->dy;
+    m.dx2 = c->dx * c->dx; m.dy2 = c->dy * c->dy;
+    m.rdx2 = 1.0 / m.dx2; m.rdy2 = 1.0 / m.dy2;
+    m.rdx = 1.0 / c->dx; m.rdy = 1.0 / c->dy;
+    m.inv_re = 1.0 / c->P.Re;
+    m.inv_dt = 1.0 / dt;
+    m.g_x = c->P.g_x; m.g_y = c->P.g_y;
+    return m;
+}
+
+// ------------------------------------------------------------------ boundary conditions
+// boundaries.c:7-39, one side per launch exactly like the reference's call sequence.
+__global__ void set_inflow_kernel(double* u, double* v, long long pitch, int ni, int nj, int side,
+                                  double u_fix, double v_fix) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x + 1;
+    double* U = u + (long long)NSB_ROW0 * pitch + NSB_COL0;
+    double* V = v + (long long)NSB_ROW0 * pitch + NSB_COL0;
+    if (side == NSB_TOP) {
+        if (t <= ni) {
+            V[(long long)nj * pitch + t] = v_fix;
+            U[(long long)(nj + 1) * pitch + t] = __dsub_rn(__dmul_rn(2.0, u_fix), U[(long long)nj * pitch + t]);
+        }
+    } else if (side == NSB_BOTTOM) {
+        if (t <= ni) {
+            V[t] = v_fix;
+            U[t] = __dsub_rn(__dmul_rn(2.0, u_fix), U[pitch + t]);
+        }
+    } else if (side == NSB_LEFT) {
+        if (t <= nj) {
+            U[(long long)t * pitch] = u_fix;
+            V[(long long)t * pitch] = __dsub_rn(__dmul_rn(2.0, v_fix), V[(long long)t * pitch + 1]);
+        }
+    } else {
+        if (t <= nj) {
+            U[(long long)t * pitch + ni] = u_fix;
+            V[(long long)t * pitch + ni + 1] = __dsub_rn(__dmul_rn(2.0, v_fix), V[(long long)t * pitch + ni]);
+        }
+    }
+}
+
+cudaError_t nsb_launch_set_inflow(nsb_ctx* c, int side, double u_fix, double v_fix) {
+    const int n = (side == NSB_TOP || side == NSB_BOTTOM) ? c->g.ni : c->g.nj;
+    set_inflow_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(c->u, c->v, c->g.pitch, c->g.ni, c->g.nj,
+                                                              side, u_fix, v_fix);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ F and G
+// Neighbour naming: c = (i,j), e = (i+1,j), w = (i-1,j), n = (i,j+1), s = (i,j-1).
+template <bool RECIP>
+__device__ __forceinline__ double lap(double c, double e, double w, double n, double s, const MomCoef& m) {
+    // d2/dx2 + d2/dy2, integration.c:57-71:  (e - 2*c + w) / (dx*dx)  +  (n - 2*c + s) / (dy*dy)
+    double two_c = __dmul_rn(2.0, c);
+    double lx = nsb_div<RECIP>(__dadd_rn(__dsub_rn(e, two_c), w), m.dx2, m.rdx2);
+    double ly = nsb_div<RECIP>(__dadd_rn(__dsub_rn(n, two_c), s), m.dy2, m.rdy2);
+    return __dadd_rn(lx, ly);
+}
+
+// integration.c:7-15 (du2_dx) and :29-37 (dv2_dy): same shape along one axis.
+//   a = 0.5(c + p), b = 0.5(q + c);  1/h (a*a - b*b) + gamma/h (|a| 0.5 (c - p) - |b| 0.5 (q - c))
+__device__ __forceinline__ double donor_self(double c, double p, double q, double inv_h, double g_h) {
+    double a = __dmul_rn(0.5, __dadd_rn(c, p));
+    double b = __dmul_rn(0.5, __dadd_rn(q, c));
+    double da = __dmul_rn(__dmul_rn(fabs(a), 0.5), __dsub_rn(c, p));
+    double db = __dmul_rn(__dmul_rn(fabs(b), 0.5), __dsub_rn(q, c));
+    return __dadd_rn(__dmul_rn(inv_h, __dsub_rn(__dmul_rn(a, a), __dmul_rn(b, b))),
+                     __dmul_rn(g_h, __dsub_rn(da, db)));
+}
+
+// integration.c:17-27 (duv_dy for F) and :39-51 (duv_dx for G): transported quantity `x` by the
+// cross velocity.  t1a+t1b is the cross-velocity pair on the far face, t2a+t2b on the near face;
+// xc the cell value, xp the far neighbour, xq the near neighbour.
+__device__ __forceinline__ double donor_cross(double t1a, double t1b, double t2a, double t2b, double xc,
+                                              double xp, double xq, double inv_h, double g_h) {
+    double a = __dmul_rn(0.5, __dadd_rn(t1a, t1b));
+    double b = __dmul_rn(0.5, __dadd_rn(t2a, t2b));
+    double fa = __dmul_rn(__dmul_rn(a, 0.5), __dadd_rn(xc, xp));
+    double fb = __dmul_rn(__dmul_rn(b, 0.5), __dadd_rn(xq, xc));
+    double da = __dmul_rn(__dmul_rn(fabs(a), 0.5), __dsub_rn(xc, xp));
+    double db = __dmul_rn(__dmul_rn(fabs(b), 0.5), __dsub_rn(xq, xc));
+    return __dadd_rn(__dmul_rn(inv_h, __dsub_rn(fa, fb)), __dmul_rn(g_h, __dsub_rn(da, db)));
+}
+
+template <bool RECIP>
+__device__ __forceinline__ double f_cell(const double* __restrict__ U, const double* __restrict__ V,
+                                         long long o, long long pitch, const MomCoef& m) {
+    const double uc = U[o], ue = U[o + 1], uw = U[o - 1], un = U[o + pitch], us = U[o - pitch];
+    const double vc = V[o], ve = V[o + 1], vs = V[o - pitch], vse = V[o - pitch + 1];
+    double visc = __dmul_rn(m.inv_re, lap<RECIP>(uc, ue, uw, un, us, m));
+    double conv_x = donor_self(uc, ue, uw, m.inv_dx, m.g_dx);                       // du2_dx
+    double conv_y = donor_cross(vc, ve, vs, vse, uc, un, us, m.inv_dy, m.g_dy);     // duv_dy
+    double rhs = __dadd_rn(__dsub_rn(__dsub_rn(visc, conv_x), conv_y), m.g_x);
+    return __dadd_rn(uc, __dmul_rn(m.dt, rhs));                                     // integration.c:78-82
+}
+
+template <bool RECIP>
+__device__ __forceinline__ double g_cell(const double* __restrict__ U, const double* __restrict__ V,
+                                         long long o, long long pitch, const MomCoef& m) {
+    const double vc = V[o], ve = V[o + 1], vw = V[o - 1], vn = V[o + pitch], vs = V[o - pitch];
+    const double uc = U[o], un = U[o + pitch], uw = U[o - 1], uwn = U[o - 1 + pitch];
+    double visc = __dmul_rn(m.inv_re, lap<RECIP>(vc, ve, vw, vn, vs, m));
+    double conv_x = donor_cross(uc, un, uw, uwn, vc, ve, vw, m.inv_dx, m.g_dx);     // duv_dx
+    double conv_y = donor_self(vc, vn, vs, m.inv_dy, m.g_dy);                       // dv2_dy
+    double rhs = __dadd_rn(__dsub_rn(__dsub_rn(visc, conv_x), conv_y), m.g_y);
+    return __dadd_rn(vc, __dmul_rn(m.dt, rhs));                                     // integration.c:86-90
+}
+
+template <bool RECIP>
+__global__ void __launch_bounds__(MB_X* MB_Y) fg_kernel(const double* __restrict__ u, const double* __restrict__ v,
+                                                         double* __restrict__ F, double* __restrict__ G,
+                                                         long long pitch, int ni, int nj, MomCoef m) {
+    const int i = blockIdx.x * MB_X + threadIdx.x + 1;
+    const int j = blockIdx.y * MB_Y + threadIdx.y + 1;
+    if (i > ni || j > nj) return;
+    const long long o = (long long)(j + NSB_ROW0) * pitch + NSB_COL0 + i;
+    if (i <= ni - 1) F[o] = f_cell<RECIP>(u, v, o, pitch, m);
+    if (j <= nj - 1) G[o] = g_cell<RECIP>(u, v, o, pitch, m);
+}
+
+cudaError_t nsb_launch_fg(nsb_ctx* c, double dt, double gamma) {
+    MomCoef m = make_mom(c, dt, gamma);
+    dim3 b(MB_X, MB_Y), g((c->g.ni + MB_X - 1) / MB_X, (c->g.nj + MB_Y - 1) / MB_Y);
+    if (c->use_recip) fg_kernel<true><<<g, b, 0, c->stream>>>(c->u, c->v, c->F, c->G, c->g.pitch, c->g.ni, c->g.nj, m);
+    else fg_kernel<false><<<g, b, 0, c->stream>>>(c->u, c->v, c->F, c->G, c->g.pitch, c->g.ni, c->g.nj, m);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ RHS (main.c:116-120)
+//   RHS = 1.0/dt * ((F - F_w)/dx + (G - G_s)/dy)
+template <bool RECIPD>
+__device__ __forceinline__ double rhs_cell(double f, double fw, double g, double gs, const MomCoef& m) {
+    double a = nsb_div<RECIPD>(__dsub_rn(f, fw), m.dx, m.rdx);
+    double b = nsb_div<RECIPD>(__dsub_rn(g, gs), m.dy, m.rdy);
+    return __dmul_rn(m.inv_dt, __dadd_rn(a, b));
+}
+
+template <bool RECIPD>
+__global__ void __launch_bounds__(MB_X* MB_Y) rhs_kernel(const double* __restrict__ F, const double* __restrict__ G,
+                                                          double* __restrict__ rhs, long long pitch, int ni, int nj,
+                                                          MomCoef m) {
+    const int i = blockIdx.x * MB_X + threadIdx.x + 1;
+    const int j = blockIdx.y * MB_Y + threadIdx.y + 1;
+    if (i > ni || j > nj) return;
+    const long long o = (long long)(j + NSB_ROW0) * pitch + NSB_COL0 + i;
+    rhs[o] = rhs_cell<RECIPD>(F[o], F[o - 1], G[o], G[o - pitch], m);
+}
+
+// exactness of 1/dx, 1/dy as reciprocals is decided on the host (nsb_ctx::recip_exact covers
+// dx2, dy2; dx, dy powers of two follow from that only when the exponents are even, so the host
+// passes a separate flag)
+static bool pow2(double x) {
+    if (!(x > 0.0)) return false;
+    int e;
+    return frexp(x, &e) == 0.5;
+}
+
+cudaError_t nsb_launch_rhs(nsb_ctx* c, double dt) {
+    MomCoef m = make_mom(c, dt, 0.0);
+    dim3 b(MB_X, MB_Y), g((c->g.ni + MB_X - 1) / MB_X, (c->g.nj + MB_Y - 1) / MB_Y);
+    const bool rd = (c->O.div_mode == NSB_DIV_RECIP) ||
+                    (c->O.div_mode == NSB_DIV_AUTO && pow2(c->dx) && pow2(c->dy));
+    if (rd) rhs_kernel<true><<<g, b, 0, c->stream>>>(c->F, c->G, c->rhs, c->g.pitch, c->g.ni, c->g.nj, m);
+    else rhs_kernel<false><<<g, b, 0, c->stream>>>(c->F, c->G, c->rhs, c->g.pitch, c->g.ni, c->g.nj, m);
+    return cudaGetLastError();
+}
+
+cudaError_t nsb_launch_fg_rhs(nsb_ctx* c, double dt, double gamma) {
+    cudaError_t e = nsb_launch_fg(c, dt, gamma);
+    if (e != cudaSuccess) return e;
+    return nsb_launch_rhs(c, dt);
+}
+
+// ------------------------------------------------------------------ velocity update + reductions
+//   u = F - dt * ((pE - p)/dx)   i <= i_max-1        main.c:133 with dp_dx integration.c:101-103
+//   v = G - dt * ((pN - p)/dy)   j <= j_max-1        main.c:134 with dp_dy integration.c:108-110
+// and, over the interior after the update: signed max u, signed max v (seeded with m[0][0] like
+// io.c:124), sum p^2.
+template <bool RECIPD, bool UPDATE>
+__global__ void __launch_bounds__(256) update_uv_kernel(double* __restrict__ u, double* __restrict__ v,
+                                                         const double* __restrict__ F, const double* __restrict__ G,
+                                                         const double* __restrict__ p, long long pitch, int ni,
+                                                         int nj, MomCoef m, double* partials, StepRed* red) {
+    __shared__ double sh[32];
+    __shared__ int is_last;
+    const int j = blockIdx.y + 1;
+    const long long ro = (long long)(j + NSB_ROW0) * pitch + NSB_COL0;
+    double mu = -1.0e300, mv = -1.0e300, sp = 0.0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x + 1; i <= ni; i += gridDim.x * blockDim.x) {
+        const long long o = ro + i;
+        const double pc = p[o];
+        double un, vn;
+        if (UPDATE) {
+            un = u[o]; vn = v[o];
+            if (i <= ni - 1) {
+                un = __dsub_rn(F[o], __dmul_rn(m.dt, nsb_div<RECIPD>(__dsub_rn(p[o + 1], pc), m.dx, m.rdx)));
+                u[o] = un;
+            }
+            if (j <= nj - 1) {
+                vn = __dsub_rn(G[o], __dmul_rn(m.dt, nsb_div<RECIPD>(__dsub_rn(p[o + pitch], pc), m.dy, m.rdy)));
+                v[o] = vn;
+            }
+        } else {
+            un = u[o]; vn = v[o];
+        }
+        mu = fmax(mu, un);
+        mv = fmax(mv, vn);
+        sp = fma(pc, pc, sp);
+    }
+    const int nblk = gridDim.x * gridDim.y;
+    const int bid = blockIdx.y * gridDim.x + blockIdx.x;
+    double bu = block_max(mu, sh);
+    double bv = block_max(mv, sh);
+    double bs = block_sum(sp, sh);
+    if (threadIdx.x == 0) {
+        partials[bid] = bu;
+        partials[nblk + bid] = bv;
+        partials[2 * nblk + bid] = bs;
+        __threadfence();
+        unsigned int t = atomicAdd(&red->ticket, 1u);
+        is_last = (t == (unsigned)nblk - 1);
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        double a = -1.0e300, b = -1.0e300, s = 0.0;
+        for (int q = threadIdx.x; q < nblk; q += blockDim.x) {
+            a = fmax(a, __ldcg(partials + q));
+            b = fmax(b, __ldcg(partials + nblk + q));
+            s += __ldcg(partials + 2 * nblk + q);
+        }
+        a = block_max(a, sh);
+        b = block_max(b, sh);
+        s = block_sum(s, sh);
+        if (threadIdx.x == 0) {
+            // io.c:124: the scan starts from m[0][0]
+            const double u00 = u[(long long)NSB_ROW0 * pitch + NSB_COL0];
+            const double v00 = v[(long long)NSB_ROW0 * pitch + NSB_COL0];
+            red->u_max = (u00 < a) ? a : u00;
+            red->v_max = (v00 < b) ? b : v00;
+            red->sum_p2 = s;
+            red->ticket = 0;
+        }
+    }
+}
+
+static void uv_grid(const nsb_ctx* c, dim3& g) {
+    g = dim3(min((c->g.ni + 255) / 256, 4), c->g.nj);
+}
+
+cudaError_t nsb_launch_update_uv(nsb_ctx* c, double dt) {
+    MomCoef m = make_mom(c, dt, 0.0);
+    dim3 g;
+    uv_grid(c, g);
+    const bool rd = (c->O.div_mode == NSB_DIV_RECIP) ||
+                    (c->O.div_mode == NSB_DIV_AUTO && pow2(c->dx) && pow2(c->dy));
+    double* p = c->pbuf[c->pcur];
+    if (rd) update_uv_kernel<true, true><<<g, 256, 0, c->stream>>>(c->u, c->v, c->F, c->G, p, c->g.pitch, c->g.ni, c->g.nj, m, c->d_red_partials, c->d_red);
+    else update_uv_kernel<false, true><<<g, 256, 0, c->stream>>>(c->u, c->v, c->F, c->G, p, c->g.pitch, c->g.ni, c->g.nj, m, c->d_red_partials, c->d_red);
+    return cudaGetLastError();
+}
+
+cudaError_t nsb_launch_reduce_uvp(nsb_ctx* c) {
+    MomCoef m = make_mom(c, 1.0, 0.0);
+    dim3 g;
+    uv_grid(c, g);
+    update_uv_kernel<true, false><<<g, 256, 0, c->stream>>>(c->u, c->v, c->F, c->G, c->pbuf[c->pcur], c->g.pitch,
+                                                            c->g.ni, c->g.nj, m, c->d_red_partials, c->d_red);
+    return cudaGetLastError();
+}

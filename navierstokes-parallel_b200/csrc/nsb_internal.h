@@ -1,0 +1,111 @@
+// nsb_internal.h -- context, HBM layout and launch prototypes shared by the .cu files.
+//
+// HBM layout (DESIGN.md "data layout"): every grid is one pitched 1-D array, x fastest.
+//   element (i, j)  ->  base[(j + ROW0) * pitch + (i + COL0)]
+// COL0 = 3 puts interior column i = 1 on a 32-byte boundary (4 doubles = one "column group", the
+// unit a thread of the streaming kernels owns); pitch is a multiple of 16 doubles (128 B) and
+// leaves >= 4 padding doubles to the right of the ghost column i_max+1, so every group load is in
+// bounds.  ROW0 = 0.  This replaces the reference's row-pointer tables (`double**`, main.cu:103-120)
+// and its j-contiguous order, which made every warp access strided.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/nsb200.h"
+
+#define NSB_COL0 3
+#define NSB_ROW0 0
+#define NSB_GROUP 4                 // doubles per column group (32 B)
+#define NSB_STRIP_GROUPS 30         // output groups per warp strip (lanes 1..30; 0 and 31 are halo)
+#define NSB_STRIP_COLS (NSB_STRIP_GROUPS * NSB_GROUP)
+
+struct NsbGrid {
+    int ni, nj;            // global interior size (i_max, j_max)
+    long long pitch;       // doubles per row
+    int rows;              // stored rows (nj + 2)
+    size_t elems;          // pitch * rows
+};
+
+// Scalars every SOR kernel needs; built on the host with the reference's operation order.
+struct SorCoef {
+    double om1;      // 1 - omega
+    double w;        // omega / (2 (1/dx2 + 1/dy2))          main.cu:493,502
+    double dx2, dy2; // delta_x^2, delta_y^2
+    double rdx2, rdy2;
+    double inv_cells_unused;
+    long long cells; // i_max * j_max
+};
+
+// Device-side control block of one SOR solve (lives in HBM; mirrored to pinned host memory).
+struct SorCtl {
+    double thresh;       // eps * (norm_p + 1.5)                main.cu:713
+    double norm_p;
+    double res;          // residual norm after the last finished iteration
+    double sum_r2;
+    int iters;           // iterations finished
+    int converged;       // set by the iteration that met the threshold
+    unsigned int ticket; // last-block election
+    int pad;
+};
+
+// Per-step reductions produced by the velocity update (and by the stand-alone reduce kernel).
+struct StepRed {
+    double u_max, v_max, sum_p2;
+    unsigned int ticket;
+    int pad;
+};
+
+struct nsb_ctx {
+    nsb_params P;
+    nsb_options O;
+    NsbGrid g;
+    int device;
+    int sm_count;
+    cudaStream_t stream;
+    bool own_stream;
+    double dx, dy;
+    bool recip_exact;      // dx2 and dy2 are powers of two -> reciprocal multiply is exact
+    bool use_recip;        // resolved division mode
+    // grids
+    double* u; double* v; double* F; double* G; double* rhs;
+    double* pbuf[2];
+    int pcur;              // pbuf[pcur] holds the current pressure
+    double* scratch;       // one grid of staging space (layout conversion)
+    // SOR machinery
+    SorCtl* d_ctl; SorCtl* h_ctl;       // device / pinned host
+    double* d_partials; int n_partials;
+    int chunk_rows, n_strips, n_chunks;
+    // step reductions
+    StepRed* d_red; StepRed* h_red;
+    double* d_red_partials; int n_red_partials;
+    bool red_valid;        // h_red holds max u, max v, sum p^2 of the current fields
+    double* h_stage; size_t h_stage_elems;   // pinned staging for uploads/downloads
+    cudaEvent_t ev0, ev1, ev_chk[2];
+    double sor_seconds;
+    int last_sor_engine;
+    char err[512];
+};
+
+static inline size_t nsb_index(const NsbGrid& g, int i, int j) {
+    return (size_t)(j + NSB_ROW0) * (size_t)g.pitch + (size_t)(i + NSB_COL0);
+}
+
+// ---- launchers (each enqueues on ctx->stream and returns the launch status) -----------------
+cudaError_t nsb_launch_set_inflow(nsb_ctx* c, int side, double u_fix, double v_fix);
+cudaError_t nsb_launch_fg(nsb_ctx* c, double dt, double gamma);
+cudaError_t nsb_launch_rhs(nsb_ctx* c, double dt);
+cudaError_t nsb_launch_fg_rhs(nsb_ctx* c, double dt, double gamma);
+cudaError_t nsb_launch_update_uv(nsb_ctx* c, double dt);
+cudaError_t nsb_launch_reduce_uvp(nsb_ctx* c);     // max u, max v, sum p^2 without updating
+cudaError_t nsb_launch_sor_begin(nsb_ctx* c);      // threshold from sum p^2, clears the flags
+cudaError_t nsb_launch_sor_stream_iter(nsb_ctx* c, int it, const double* pin, double* pout, int check);
+cudaError_t nsb_launch_sor_simple_iter(nsb_ctx* c, int it, double* p, int check);
+cudaError_t nsb_launch_sor_finish_ghosts(nsb_ctx* c, double* pfinal, const double* pprev);
+cudaError_t nsb_launch_to_xfast(nsb_ctx* c, const double* src_ref, double* dst);   // [i][j] -> grid
+cudaError_t nsb_launch_from_xfast(nsb_ctx* c, const double* src, double* dst_ref); // grid -> [i][j]
+cudaError_t nsb_launch_pack_xfast(nsb_ctx* c, const double* src, double* dst_dense, int to_dense);
+int nsb_sor_resident_supported(const nsb_ctx* c);
+cudaError_t nsb_launch_sor_resident(nsb_ctx* c, int max_it, int check);
+
+void nsb_sor_plan(nsb_ctx* c);

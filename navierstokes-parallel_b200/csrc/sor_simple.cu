@@ -1,0 +1,164 @@
+// sor_simple.cu -- SOR bookkeeping kernels and the launch-per-phase validation engine.
+//
+// NSB_SOR_SIMPLE restates src/parallel/main.cu:684-706 literally with stored ghosts and one launch
+// per phase (ghost refresh, colour 0, ghost refresh, colour 1, residual).  It exists to check the
+// fused engines against an independent GPU implementation at sizes the CPU oracle cannot reach
+// (tests/test_gpu_parity.py); it is coalesced (x fastest) but makes no attempt to be fast.
+#include "nsb_internal.h"
+#include "nsb_math.cuh"
+
+// ---- SOR entry: threshold from the cached sum p^2 (replaces calculate_L2_norm_device,
+//      main.cu:626-653 and the host test of main.cu:713)
+__global__ void sor_begin_kernel(SorCtl* ctl, const StepRed* red, double eps, long long cells) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        double norm_p = sqrt(red->sum_p2 / (double)cells);      // main.cu:588
+        ctl->norm_p = norm_p;
+        ctl->thresh = eps * (norm_p + 1.5);
+        ctl->res = 0.0;
+        ctl->sum_r2 = 0.0;
+        ctl->iters = 0;
+        ctl->converged = 0;
+        ctl->ticket = 0;
+    }
+}
+
+cudaError_t nsb_launch_sor_begin(nsb_ctx* c) {
+    sor_begin_kernel<<<1, 32, 0, c->stream>>>(c->d_ctl, c->d_red, c->P.epsilon,
+                                              (long long)c->g.ni * (long long)c->g.nj);
+    return cudaGetLastError();
+}
+
+// ---- Neumann ghosts, main.cu:249-273 (corner copies there are racy and never read: skipped)
+__global__ void ghost_refresh_kernel(double* p, long long pitch, int ni, int nj, const SorCtl* ctl) {
+    if (ctl && *((volatile const int*)&ctl->converged)) return;
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    double* base = p + (long long)NSB_ROW0 * pitch + NSB_COL0;
+    if (t < nj) {
+        int j = t + 1;
+        base[(long long)j * pitch + 0] = base[(long long)j * pitch + 1];
+        base[(long long)j * pitch + ni + 1] = base[(long long)j * pitch + ni];
+    }
+    if (t < ni) {
+        int i = t + 1;
+        base[i] = base[pitch + i];
+        base[(long long)(nj + 1) * pitch + i] = base[(long long)nj * pitch + i];
+    }
+}
+
+template <bool RECIP>
+__global__ void sor_color_kernel(double* p, const double* __restrict__ rhs, long long pitch, int ni,
+                                 int nj, int color, SorCoef k, const SorCtl* ctl) {
+    if (ctl && *((volatile const int*)&ctl->converged)) return;
+    // thread -> one cell of the colour: x index over half-rows
+    int half = blockIdx.x * blockDim.x + threadIdx.x;     // 0 .. ceil(ni/2)-1
+    int j = blockIdx.y + 1;
+    int i = 2 * half + 1 + ((1 + j + color) & 1);         // first i with (i + j) % 2 == color
+    if (i > ni) return;
+    double* row = p + (long long)(j + NSB_ROW0) * pitch + NSB_COL0;
+    double pc = row[i];
+    double v = sor_cell<RECIP>(pc, row[i + 1], row[i - 1], row[i + pitch], row[i - pitch],
+                               rhs[(long long)(j + NSB_ROW0) * pitch + NSB_COL0 + i], k);
+    row[i] = v;
+}
+
+template <bool RECIP>
+__global__ void sor_residual_kernel(const double* __restrict__ p, const double* __restrict__ rhs,
+                                    long long pitch, int ni, int nj, SorCoef k, double* partials,
+                                    SorCtl* ctl, int it, int check) {
+    __shared__ double sh[32];
+    __shared__ int is_last;
+    if (check && *((volatile int*)&ctl->converged)) return;
+    int j = blockIdx.y + 1;
+    const double* row = p + (long long)(j + NSB_ROW0) * pitch + NSB_COL0;
+    const double* rrow = rhs + (long long)(j + NSB_ROW0) * pitch + NSB_COL0;
+    double acc = 0.0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x + 1; i <= ni; i += gridDim.x * blockDim.x) {
+        double q = sor_residual<RECIP>(row[i], row[i + 1], row[i - 1], row[i + pitch], row[i - pitch],
+                                       rrow[i], k);
+        acc = fma(q, q, acc);
+    }
+    double tot = block_sum(acc, sh);
+    const int nblk = gridDim.x * gridDim.y;
+    if (threadIdx.x == 0) {
+        partials[blockIdx.y * gridDim.x + blockIdx.x] = tot;
+        __threadfence();
+        unsigned int t = atomicAdd(&ctl->ticket, 1u);
+        is_last = (t == (unsigned)nblk - 1);
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        double s = 0.0;
+        for (int q = threadIdx.x; q < nblk; q += blockDim.x) s += __ldcg(partials + q);
+        double total = block_sum(s, sh);
+        if (threadIdx.x == 0) {
+            double res = sqrt(total / (double)k.cells);
+            ctl->sum_r2 = total;
+            ctl->res = res;
+            ctl->iters = it + 1;
+            if (res <= ctl->thresh) ctl->converged = 1;
+            ctl->ticket = 0;
+        }
+    }
+}
+
+static SorCoef make_coef(const nsb_ctx* c) {
+    SorCoef k;
+    const double dx2 = c->dx * c->dx, dy2 = c->dy * c->dy;
+    k.om1 = 1.0 - c->P.omega;
+    k.w = c->P.omega / (2.0 * (1.0 / dx2 + 1.0 / dy2));
+    k.dx2 = dx2; k.dy2 = dy2; k.rdx2 = 1.0 / dx2; k.rdy2 = 1.0 / dy2;
+    k.inv_cells_unused = 0.0;
+    k.cells = (long long)c->g.ni * (long long)c->g.nj;
+    return k;
+}
+
+// One full iteration in place on p.  With `check`, every kernel of an iteration queued after the
+// converged flag was raised returns at once, so p stays the converged iterate.
+cudaError_t nsb_launch_sor_simple_iter(nsb_ctx* c, int it, double* p, int check) {
+    const SorCtl* ck = check ? c->d_ctl : nullptr;
+    const int ni = c->g.ni, nj = c->g.nj;
+    const SorCoef k = make_coef(c);
+    const int nb = (max(ni, nj) + 255) / 256;
+    const int half = (ni + 1) / 2;
+    dim3 cgrid((half + 127) / 128, nj);
+    dim3 rgrid(min((ni + 255) / 256, 8), nj);
+    // partials: one per residual block; the streaming plan always allocates >= 8 * nj + 64
+    for (int color = 0; color < 2; color++) {
+        ghost_refresh_kernel<<<nb, 256, 0, c->stream>>>(p, c->g.pitch, ni, nj, ck);
+        if (c->use_recip) sor_color_kernel<true><<<cgrid, 128, 0, c->stream>>>(p, c->rhs, c->g.pitch, ni, nj, color, k, ck);
+        else sor_color_kernel<false><<<cgrid, 128, 0, c->stream>>>(p, c->rhs, c->g.pitch, ni, nj, color, k, ck);
+    }
+    if (c->use_recip) sor_residual_kernel<true><<<rgrid, 256, 0, c->stream>>>(p, c->rhs, c->g.pitch, ni, nj, k, c->d_partials, c->d_ctl, it, check);
+    else sor_residual_kernel<false><<<rgrid, 256, 0, c->stream>>>(p, c->rhs, c->g.pitch, ni, nj, k, c->d_partials, c->d_ctl, it, check);
+    return cudaGetLastError();
+}
+
+// ---- ghosts of the final pressure for the fused engines.  The reference leaves in the ghost
+// cells what the refresh BEFORE the last black sweep copied (main.cu:694): the current value of a
+// wall-adjacent red cell, the pre-black value of a wall-adjacent black cell.  The pre-black value
+// of the last iteration is what the other ping-pong buffer still holds.
+__global__ void sor_finish_ghosts_kernel(double* pf, const double* __restrict__ pv, long long pitch,
+                                         int ni, int nj) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    double* f = pf + (long long)NSB_ROW0 * pitch + NSB_COL0;
+    const double* v = pv + (long long)NSB_ROW0 * pitch + NSB_COL0;
+    if (t < nj) {
+        int j = t + 1;
+        long long r = (long long)j * pitch;
+        f[r + 0] = ((1 + j) & 1) ? v[r + 1] : f[r + 1];
+        f[r + ni + 1] = ((ni + j) & 1) ? v[r + ni] : f[r + ni];
+    }
+    if (t < ni) {
+        int i = t + 1;
+        f[i] = ((i + 1) & 1) ? v[pitch + i] : f[pitch + i];
+        long long r = (long long)nj * pitch;
+        f[r + pitch + i] = ((i + nj) & 1) ? v[r + i] : f[r + i];
+    }
+}
+
+cudaError_t nsb_launch_sor_finish_ghosts(nsb_ctx* c, double* pfinal, const double* pprev) {
+    const int n = max(c->g.ni, c->g.nj);
+    sor_finish_ghosts_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(pfinal, pprev, c->g.pitch, c->g.ni, c->g.nj);
+    return cudaGetLastError();
+}

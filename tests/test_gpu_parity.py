@@ -1,0 +1,384 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the CPU oracle.
+
+Bars (DESIGN.md "parity"):
+  * F, G, RHS, u, v, p fields: BIT-EXACT against the oracle with the same sweep order (the kernels
+    use non-contracting FP64 intrinsics in the reference's association order);
+  * SOR iteration counts and the dt sequence: EQUAL;
+  * residual norm / norm_p (order-dependent sums): relative 1e-12;
+  * against the serial (lexicographic) order at tight eps: u, v and mean-free p within 1e-8
+    relative (north_star's tolerance).
+"""
+import ctypes as C
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import binding as ob
+from util import ROOT, nsb
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _solver(m, engine=None, **kw):
+    P = m.make_params(**kw)
+    eng = m.SOR_STREAM if engine is None else engine
+    return m.Solver(P, sor_engine=eng), P
+
+
+def _orc_params(P):
+    return ob.make_params(**{k: getattr(P, k) for k, _ in ob.Params._fields_})
+
+
+def _rand(shape, seed):
+    return np.ascontiguousarray(np.random.default_rng(seed).uniform(-1, 1, shape))
+
+
+# ------------------------------------------------------------------------------- phases
+
+@pytest.mark.parametrize("ni,nj,a,b", [(16, 16, 1.0, 1.0), (37, 23, 1.3, 0.7), (130, 5, 1.0, 1.0), (5, 250, 2.0, 1.0)])
+def test_bc_fg_rhs_update_bit_exact(ni, nj, a, b):
+    m = nsb()
+    s, P = _solver(m, i_max=ni, j_max=nj, a=a, b=b, Re=77.0, g_x=0.05, g_y=-0.03)
+    L = ob.lib()
+    u, v, p = _rand(s.shape, 1), _rand(s.shape, 2), _rand(s.shape, 3)
+    s.upload(m.U, u); s.upload(m.V, v); s.upload(m.P, p)
+    dx, dy = a / ni, b / nj
+    dt, gamma = 0.0123, 0.41
+    # max_mat (signed, seeded with m[0][0])
+    um, vm = s.max_mat()
+    assert um == L.orc_max_mat(ni, nj, ob._ptr(u)) and vm == L.orc_max_mat(ni, nj, ob._ptr(v))
+    # dt / gamma: host arithmetic in the reference's order
+    dtg = s.dt_gamma(um, vm)
+    odt, og = C.c_double(), C.c_double()
+    L.orc_dt_gamma(C.byref(_orc_params(P)), dx, dy, um, vm, C.byref(odt), C.byref(og))
+    assert dtg == (odt.value, og.value)
+    # every side, non-trivial inflow
+    for side in (m.LEFT, m.RIGHT, m.BOTTOM, m.TOP):
+        s.set_inflow(side, 0.75, -0.25)
+        L.orc_set_inflow(ni, nj, ob._ptr(u), ob._ptr(v), side, 0.75, -0.25)
+    assert np.array_equal(s.download(m.U), u) and np.array_equal(s.download(m.V), v)
+    # F, G  (untouched cells keep their previous content, here zero, like the reference)
+    s.FG(dt, gamma)
+    F, G = np.zeros_like(u), np.zeros_like(u)
+    L.orc_FG(ob._ptr(F), ob._ptr(G), ob._ptr(u), ob._ptr(v), ni, nj, P.Re, P.g_x, P.g_y, dt, dx, dy, gamma)
+    assert np.array_equal(s.download(m.F), F)
+    assert np.array_equal(s.download(m.G), G)
+    # RHS
+    s.RHS(dt)
+    R = np.zeros_like(u)
+    L.orc_RHS(ob._ptr(R), ob._ptr(F), ob._ptr(G), ni, nj, dt, dx, dy)
+    assert np.array_equal(s.download(m.RHS), R)
+    # velocity update + the reductions it refreshes
+    s.update_uv(dt)
+    L.orc_update_uv(ob._ptr(u), ob._ptr(v), ob._ptr(F), ob._ptr(G), ob._ptr(p), ni, nj, dt, dx, dy)
+    assert np.array_equal(s.download(m.U), u) and np.array_equal(s.download(m.V), v)
+    um, vm = s.max_mat()
+    assert um == L.orc_max_mat(ni, nj, ob._ptr(u)) and vm == L.orc_max_mat(ni, nj, ob._ptr(v))
+    s.close()
+
+
+def test_layout_roundtrip_both_layouts():
+    m = nsb()
+    s, P = _solver(m, i_max=45, j_max=70)
+    a = _rand(s.shape, 9)
+    s.upload(m.P, a, m.LAYOUT_REF)
+    assert np.array_equal(s.download(m.P, m.LAYOUT_REF), a)
+    assert np.array_equal(s.download(m.P, m.LAYOUT_XFAST), a.T)
+    s.upload(m.U, np.ascontiguousarray(a.T), m.LAYOUT_XFAST)
+    assert np.array_equal(s.download(m.U, m.LAYOUT_REF), a)
+    s.close()
+
+
+# ------------------------------------------------------------------------------- SOR
+
+SOR_SHAPES = [(8, 8), (16, 16), (31, 17), (120, 40), (121, 33), (257, 64), (64, 300), (500, 7), (3, 3), (1, 9), (9, 1)]
+
+
+@pytest.mark.parametrize("engine", ["stream", "simple"])
+@pytest.mark.parametrize("ni,nj", SOR_SHAPES)
+def test_sor_per_iteration_bit_exact(engine, ni, nj):
+    """p after 1, 2, 3, +5 iterations equals the oracle's red-black iterate bit for bit, residual
+    norm to 1e-12 relative; sizes include non-multiples of every tile dimension (the reference's
+    CUDA kernel is wrong for those)."""
+    m = nsb()
+    eng = dict(stream=m.SOR_STREAM, simple=m.SOR_SIMPLE)[engine]
+    a, b = 1.0, 0.9
+    s, P = _solver(m, engine=eng, i_max=ni, j_max=nj, a=a, b=b, omega=1.7)
+    L = ob.lib()
+    p = _rand(s.shape, 11) * 0.5
+    rhs = _rand(s.shape, 12) * 3.0
+    s.upload(m.P, p); s.upload(m.RHS, rhs)
+    dx, dy = a / ni, b / nj
+    for n in (1, 1, 1, 5):
+        r_gpu = s.sor_iterations(n)
+        for _ in range(n):
+            r_cpu = L.orc_SOR_rb_iter(ob._ptr(p), ni, nj, dx, dy, ob._ptr(rhs), P.omega)
+        got = s.download(m.P)
+        assert np.array_equal(got[1:-1, 1:-1], p[1:-1, 1:-1])
+        # ghosts (non-corner) hold what the refresh before the last black sweep copied
+        assert np.array_equal(got[0, 1:-1], p[0, 1:-1]) and np.array_equal(got[-1, 1:-1], p[-1, 1:-1])
+        assert np.array_equal(got[1:-1, 0], p[1:-1, 0]) and np.array_equal(got[1:-1, -1], p[1:-1, -1])
+        assert abs(r_gpu - r_cpu) <= 1e-12 * abs(r_cpu)
+    s.close()
+
+
+@pytest.mark.parametrize("div_mode", ["exact", "recip"])
+def test_sor_division_modes(div_mode):
+    """Non power-of-two spacing: NSB_DIV_EXACT (and AUTO) is bit-exact; NSB_DIV_RECIP stays within
+    the stated 1e-8 relative tolerance."""
+    m = nsb()
+    ni, nj, a, b = 50, 30, 1.0, 1.0
+    P = m.make_params(i_max=ni, j_max=nj, a=a, b=b)
+    s = m.Solver(P, sor_engine=m.SOR_STREAM, div_mode=dict(exact=m.DIV_EXACT, recip=m.DIV_RECIP)[div_mode])
+    p, rhs = _rand(s.shape, 21), _rand(s.shape, 22)
+    s.upload(m.P, p); s.upload(m.RHS, rhs)
+    s.sor_iterations(20)
+    for _ in range(20):
+        ob.lib().orc_SOR_rb_iter(ob._ptr(p), ni, nj, a / ni, b / nj, ob._ptr(rhs), P.omega)
+    got = s.download(m.P)[1:-1, 1:-1]
+    if div_mode == "exact":
+        assert np.array_equal(got, p[1:-1, 1:-1])
+    else:
+        assert np.max(np.abs(got - p[1:-1, 1:-1])) <= 1e-8 * np.max(np.abs(p))
+    s.close()
+
+
+@pytest.mark.parametrize("engine", ["stream", "simple"])
+def test_sor_convergence_iteration_count(engine):
+    """Converged solve: same iteration count, same return value (it+1), bit-equal p; then the
+    not-converged contract (-1, p = last iterate)."""
+    m = nsb()
+    eng = dict(stream=m.SOR_STREAM, simple=m.SOR_SIMPLE)[engine]
+    ni, nj = 48, 40
+    s, P = _solver(m, engine=eng, i_max=ni, j_max=nj, epsilon=1e-5, max_it=5000)
+    p = np.zeros(s.shape)
+    x = (np.arange(ni + 2) - 0.5) / ni
+    y = (np.arange(nj + 2) - 0.5) / nj
+    rhs = np.ascontiguousarray(np.cos(np.pi * x)[:, None] * np.cos(np.pi * y)[None, :])
+    s.upload(m.P, p); s.upload(m.RHS, rhs)
+    ret, its, res, n0 = s.SOR()
+    oret, oits, ores, on0 = ob.sor_rb(p, rhs, 1.0 / ni, 1.0 / nj, P.omega, P.epsilon, P.max_it)
+    assert (ret, its) == (oret, oits) and ret > 0
+    assert np.array_equal(s.download(m.P)[1:-1, 1:-1], p[1:-1, 1:-1])
+    assert abs(res - ores) <= 1e-12 * ores and n0 == on0
+    s.close()
+    # max_it too small
+    s, P = _solver(m, engine=eng, i_max=ni, j_max=nj, epsilon=1e-9, max_it=37)
+    p = np.zeros(s.shape)
+    s.upload(m.P, p); s.upload(m.RHS, rhs)
+    ret, its, res, n0 = s.SOR()
+    oret, oits, ores, on0 = ob.sor_rb(p, rhs, 1.0 / ni, 1.0 / nj, P.omega, P.epsilon, P.max_it)
+    assert ret == oret == -1 and its == oits == 37
+    assert np.array_equal(s.download(m.P)[1:-1, 1:-1], p[1:-1, 1:-1])
+    s.close()
+
+
+# ------------------------------------------------------------------------------- whole runs
+
+def _compare_run(m, c, engine):
+    P = m.make_params(**c["params"])
+    s = m.Solver(P, sor_engine=engine)
+    log, t_end = s.run()
+    assert len(log) == c["steps"]
+    assert [x["sor_iters"] for x in log] == c["sor_iters"]
+    assert [x["sor_ret"] for x in log] == c["sor_ret"]
+    assert [float(x["dt"]).hex() for x in log] == c["dt_hex"]
+    ref = np.load(os.path.join(GOLD, c["fields"]))
+    for name, fid in (("u", m.U), ("v", m.V), ("p", m.P)):
+        got = s.download(fid)
+        want = ref[name]
+        if name == "p":       # corner ghosts are unspecified in the reference (racy copies)
+            got, want = got.copy(), want.copy()
+            for arr in (got, want):
+                arr[0, 0] = arr[0, -1] = arr[-1, 0] = arr[-1, -1] = 0.0
+        assert np.array_equal(got, want), (c["name"], name)
+    uc, vc = s.center()
+    assert float(uc).hex() == c["u_center_hex"] and float(vc).hex() == c["v_center_hex"]
+    s.close()
+
+
+@pytest.mark.parametrize("engine", ["stream", "simple"])
+def test_whole_run_matches_committed_redblack_fixtures(engine):
+    m = nsb()
+    eng = dict(stream=m.SOR_STREAM, simple=m.SOR_SIMPLE)[engine]
+    cases = [c for c in json.load(open(os.path.join(GOLD, "runs.json"))) if c["sor_order"] == 1]
+    assert len(cases) >= 4
+    for c in cases:
+        _compare_run(m, c, eng)
+
+
+def test_whole_run_vs_live_oracle_nonsquare_gravity():
+    m = nsb()
+    kw = dict(i_max=70, j_max=45, a=1.4, b=0.9, T=0.3, Re=200.0, g_x=0.02, g_y=-0.05, tau=0.8, max_it=400)
+    s, P = _solver(m, **kw)
+    log, _ = s.run()
+    o = ob.run(ob.make_params(**kw), sor_order=1)
+    assert [x["sor_iters"] for x in log] == [x["sor_iters"] for x in o["log"]]
+    assert [x["dt"] for x in log] == [x["dt"] for x in o["log"]]
+    for name, fid in (("u", m.U), ("v", m.V)):
+        assert np.array_equal(s.download(fid), o[name])
+    assert np.array_equal(s.download(m.P)[1:-1, 1:-1], o["p"][1:-1, 1:-1])
+    s.close()
+
+
+def test_serial_order_agreement_at_tight_eps():
+    """north_star: <= 1e-8 relative max-abs difference to the serial C solver after convergence
+    to the same (tight) eps.  p is compared mean-free (pure Neumann problem)."""
+    m = nsb()
+    kw = dict(i_max=32, j_max=32, T=0.6, epsilon=1e-10, max_it=200000)
+    s, P = _solver(m, **kw)
+    log, _ = s.run()
+    o = ob.run(ob.make_params(**kw), sor_order=0)
+    assert len(log) == o["steps"]
+    for name, fid in (("u", m.U), ("v", m.V)):
+        a, b = s.download(fid), o[name]
+        assert np.max(np.abs(a - b)) <= 1e-8 * np.max(np.abs(b))
+    a, b = s.download(m.P)[1:-1, 1:-1], o["p"][1:-1, 1:-1]
+    a, b = a - a.mean(), b - b.mean()
+    assert np.max(np.abs(a - b)) <= 1e-8 * np.max(np.abs(b))
+    s.close()
+
+
+def test_unknown_problem_type_is_an_error():
+    m = nsb()
+    s, P = _solver(m, i_max=8, j_max=8, problem=3)
+    with pytest.raises(m.NsbError):
+        s.step(0.0)
+    s.close()
+
+
+# ------------------------------------------------------------------------------- size-independent properties
+
+def test_stream_engine_equals_simple_engine_at_scale():
+    """At a size the CPU oracle cannot reach quickly: the fused streaming pass and the literal
+    launch-per-phase engine must produce the same bits."""
+    m = nsb()
+    ni, nj = 2048, 1536
+    outs = []
+    for eng in (m.SOR_STREAM, m.SOR_SIMPLE):
+        s, P = _solver(m, engine=eng, i_max=ni, j_max=nj)
+        s.upload(m.P, _rand(s.shape, 31)); s.upload(m.RHS, _rand(s.shape, 32))
+        r = s.sor_iterations(7)
+        outs.append((s.download(m.P)[1:-1, 1:-1], r))
+        s.close()
+    assert np.array_equal(outs[0][0], outs[1][0])
+    assert abs(outs[0][1] - outs[1][1]) <= 1e-12 * outs[1][1]
+
+
+def test_sor_linearity_and_constant_nullspace():
+    """SOR is affine in (p, RHS): with RHS = 0, iterating a*p gives a*iterate(p) for a power of
+    two (exact in FP64); a constant field is a fixed point with zero residual."""
+    m = nsb()
+    ni, nj = 300, 200
+    s, P = _solver(m, i_max=ni, j_max=nj)
+    p = _rand(s.shape, 41)
+    zero = np.zeros(s.shape)
+    s.upload(m.RHS, zero)
+    s.upload(m.P, p); s.sor_iterations(6); a = s.download(m.P)[1:-1, 1:-1]
+    s.upload(m.P, 4.0 * p); s.sor_iterations(6); b = s.download(m.P)[1:-1, 1:-1]
+    assert np.array_equal(4.0 * a, b)
+    s.upload(m.P, np.full(s.shape, 3.25)); r = s.sor_iterations(3)
+    assert np.all(s.download(m.P)[1:-1, 1:-1] == 3.25) and r == 0.0
+    s.close()
+
+
+# ------------------------------------------------------------------------------- host-grid API, driver, output
+
+def test_host_grid_api_SOR_and_FG():
+    m = nsb()
+    L = m.lib()
+    ni, nj = 40, 24
+    dx, dy = 1.0 / ni, 1.0 / nj
+    p, rhs = _rand((ni + 2, nj + 2), 51) * 0.1, _rand((ni + 2, nj + 2), 52)
+    rhs[1:-1, 1:-1] -= rhs[1:-1, 1:-1].mean()
+    q = p.copy()
+    res = np.zeros_like(p)
+    it, lr = C.c_int(), C.c_double()
+    rc = L.nsb_SOR_iters(m.rows(q), ni, nj, dx, dy, m.rows(res), m.rows(rhs), 1.7, 1e-6, 3000, C.byref(it), C.byref(lr))
+    oret, oits, ores, _ = ob.sor_rb(p, rhs, dx, dy, 1.7, 1e-6, 3000)
+    assert rc == oret and it.value == oits
+    assert np.array_equal(q[1:-1, 1:-1], p[1:-1, 1:-1])
+    # serial-style return code
+    q2 = np.zeros_like(p)
+    assert L.nsb_SOR(m.rows(q2), ni, nj, dx, dy, m.rows(res), m.rows(rhs), 1.7, 1e-6, 3000) == 0
+    assert L.nsb_SOR(m.rows(q2), ni, nj, dx, dy, m.rows(res), m.rows(rhs), 1.7, 1e-14, 3) == -1
+    # FG on jagged grids: u has i_max+1 rows, v rows have j_max+1 entries
+    u = _rand((ni + 1, nj + 2), 53)
+    v = _rand((ni + 2, nj + 1), 54)
+    F, G = np.zeros((ni + 2, nj + 2)), np.zeros((ni + 2, nj + 2))
+    assert L.nsb_FG(m.rows(F), m.rows(G), m.rows(u), m.rows(v), ni, nj, 100.0, 0.0, 0.0, 0.01, dx, dy, 0.3) == 0
+    uf, vf = np.zeros((ni + 2, nj + 2)), np.zeros((ni + 2, nj + 2))
+    uf[:ni + 1] = u; vf[:, :nj + 1] = v
+    F2, G2 = np.zeros_like(F), np.zeros_like(F)
+    ob.lib().orc_FG(ob._ptr(F2), ob._ptr(G2), ob._ptr(uf), ob._ptr(vf), ni, nj, 100.0, 0.0, 0.0, 0.01, dx, dy, 0.3)
+    assert np.array_equal(F, F2) and np.array_equal(G, G2)
+    assert L.nsb_max_mat(ni, nj, m.rows(u)) == ob.lib().orc_max_mat(ni, nj, ob._ptr(uf))
+    L.nsb_host_api_reset()
+
+
+def test_host_grid_timestep_equals_context_run():
+    m = nsb()
+    L = m.lib()
+    kw = dict(i_max=32, j_max=32, T=1.5)
+    P = m.make_params(**kw)
+    ni, nj = P.i_max, P.j_max
+    u, v = np.zeros((ni + 1, nj + 2)), np.zeros((ni + 2, nj + 1))
+    p, F, G, R = (np.zeros((ni + 2, nj + 2)) for _ in range(4))
+    t, its = 0.0, []
+    while t < P.T:
+        info = m.StepInfo()
+        assert L.nsb_timestep(C.byref(P), t, m.rows(u), m.rows(v), m.rows(p), m.rows(F), m.rows(G), m.rows(R), C.byref(info)) == 0
+        its.append(info.sor_iters)
+        t += info.dt
+    L.nsb_host_api_reset()
+    c = [c for c in json.load(open(os.path.join(GOLD, "runs.json"))) if c["name"] == "rb_32"][0]
+    assert its == c["sor_iters"]
+    ref = np.load(os.path.join(GOLD, c["fields"]))
+    assert np.array_equal(u, ref["u"][:ni + 1]) and np.array_equal(v, ref["v"][:, :nj + 1])
+    assert np.array_equal(p[1:-1, 1:-1], ref["p"][1:-1, 1:-1])
+
+
+def test_output_files_match_reference_format(tmp_path):
+    """io.c:61-120 text format incl. its quirks, byte for byte against the oracle's writer (which is
+    pinned to the reference's output() in test_oracle_output)."""
+    m = nsb()
+    kw = dict(i_max=12, j_max=9, T=0.5, a=1.0, b=0.75)
+    s, P = _solver(m, **kw)
+    log, t_end = s.run()
+    (tmp_path / "g").mkdir(); (tmp_path / "o").mkdir()
+    s.output(t_end, str(tmp_path / "g" / "0"))
+    u, v, p = s.download(m.U), s.download(m.V), s.download(m.P)
+    ob.lib().orc_output(P.i_max, P.j_max, ob._ptr(u), ob._ptr(v), ob._ptr(p), t_end, P.a, P.b, str(tmp_path / "o" / "0").encode())
+    for suf in ("_u.txt", "_v.txt", "_p.txt"):
+        assert (tmp_path / "g" / ("0" + suf)).read_bytes() == (tmp_path / "o" / ("0" + suf)).read_bytes()
+    txt = (tmp_path / "g" / "0_u.txt").read_text().splitlines()
+    assert len(txt) == 3 + P.j_max + 2 and len(txt[3].split()) == P.i_max + 1
+    assert txt[-1].split()[-1] == "2.00000"          # u[i_max][j_max+1] = 2 quirk
+    s.close()
+
+
+def test_c_driver_process_contract(tmp_path):
+    """build/parallel: same stdout lines as the serial reference binary at %.6f, stderr ends with
+    the SOR seconds and no newline."""
+    exe = os.path.join(ROOT, "build", "parallel")
+    assert os.path.exists(exe)
+    f = tmp_path / "case.in"
+    f.write_text("1\n1\n64\n64\n1.0\n1.0\n0.1\n1000.0\n0.0\n0.0\n1.0\n1.7\n0.0001\n20000\n1\n")
+    out = subprocess.run([exe, str(f), "16"], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    o = ob.run(ob.make_params(i_max=64, j_max=64, T=0.1), sor_order=1)
+    assert out.stdout == "U-CENTER: %.6f\nV-CENTER: %.6f\n" % (o["u"][32, 32], o["v"][32, 32])
+    last = out.stderr.splitlines()[-1]
+    assert not out.stderr.endswith("\n") and float(last) > 0.0
+    if ob.have_ref():
+        ref = subprocess.run([ob.REF_SERIAL, str(f)], capture_output=True, text=True)
+        # the reference's own acceptance rule (colab-runner.ipynb cell 4): tokens within 1e-4
+        for a, b in zip(out.stdout.split(), ref.stdout.split()):
+            try:
+                assert abs(float(a) - float(b)) <= 1e-4
+            except ValueError:
+                assert a == b

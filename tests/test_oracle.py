@@ -197,3 +197,32 @@ def test_redblack_ghost_free_statement():
                 r = (e - 2.0 * w[i, j] + ww) / dx2 + (n - 2.0 * w[i, j] + s) / dy2 - rhs[i, j]
                 acc += r * r
         assert math.sqrt(acc / (ni * nj)) == r_or
+
+
+@needs_ref
+def test_oracle_output_matches_reference_output(tmp_path, monkeypatch):
+    """io.c:61-120: byte-identical files, on jagged grids shaped like the reference allocates."""
+    R = ob.ref()
+    ni, nj = 7, 5
+    rng = np.random.default_rng(3)
+    u, v, p = (np.ascontiguousarray(rng.uniform(-2, 2, (ni + 2, nj + 2))) for _ in range(3))
+    (tmp_path / "a").mkdir(); (tmp_path / "b").mkdir()
+    monkeypatch.chdir(tmp_path)     # the reference builds file names in char[64] (io.c:65-76): keep the prefix short
+    assert ob.lib().orc_output(ni, nj, ob._ptr(u), ob._ptr(v), ob._ptr(p), 0.123456, 1.0, 2.0, b"a/x") == 0
+    uj = np.ascontiguousarray(u[:ni + 1])
+    R.output(ni, nj, ob.rows(uj), ob.rows(v), ob.rows(p), 0.123456, 1.0, 2.0, b"b/x")
+    for suf in ("_u.txt", "_v.txt", "_p.txt"):
+        assert (tmp_path / "a" / ("x" + suf)).read_bytes() == (tmp_path / "b" / ("x" + suf)).read_bytes()
+    assert ob.lib().orc_output(ni, nj, ob._ptr(u), ob._ptr(v), ob._ptr(p), 0.0, 1.0, 1.0, b"/nonexistent_dir/x") == -1
+
+
+def test_redblack_omp_variant_equals_sequential():
+    ni, nj = 40, 33
+    rng = np.random.default_rng(8)
+    p = np.ascontiguousarray(rng.uniform(-1, 1, (ni + 2, nj + 2)))
+    rhs = np.ascontiguousarray(rng.uniform(-1, 1, (ni + 2, nj + 2)))
+    q = p.copy()
+    a = ob.sor_rb(p, rhs, 1.0 / ni, 1.0 / nj, 1.7, 1e-30, 25)
+    b = ob.sor_rb_omp(q, rhs, 1.0 / ni, 1.0 / nj, 1.7, 1e-30, 25, 4)
+    assert a[0] == b[0] == -1 and np.array_equal(p, q)
+    assert abs(a[2] - b[2]) <= 1e-12 * a[2]
