@@ -96,7 +96,7 @@ __device__ __forceinline__ void sor_step(double (&P)[SOR_WINDOW][4], double (&R)
     {
         const int rp = j + SOR_AHEAD, rr = j + SOR_AHEAD - 1;
         load_group(P[sPF], pin_col + (long long)rp * a.pitch, col_ok && rp >= 0 && rp <= a.nj + 1 && rp <= jc1 + 3);
-        load_group(R[sRF], rhs_col + (long long)rr * a.pitch, col_ok && rr >= 1 && rr <= a.nj && rr <= jc1 + 1);
+        load_group(R[sRF], rhs_col + (long long)rr * a.pitch, col_ok && rr >= 1 && rr <= a.nj && rr <= jc1 + 2);
     }
 
     // ---- colour 0 (red) on row D = j-1, neighbours: C (j-2, black cells still old), E (j)
