@@ -125,7 +125,8 @@ def lib():
         if not os.path.exists(LIB_PATH):
             raise NsbError(f"{LIB_PATH} is missing: run __graft_entry__.build() / make -C "
                            f"{os.path.join(HERE, 'csrc')}.  There is no CPU fallback.")
-        L = C.CDLL(LIB_PATH)
+        # NSB200_LIB: developer hook to load a tuning variant of the same library (tools/build_variants.sh)
+        L = C.CDLL(os.environ.get("NSB200_LIB") or LIB_PATH)
         for name, (res, args) in ABI.items():
             fn = getattr(L, name)
             fn.restype = res

@@ -130,7 +130,7 @@ extern "C" int nsb_create(const nsb_params* P, const nsb_options* opt, nsb_ctx**
     // pitch: COL0 + (ni+2) columns + one spare group, rounded up to 16 doubles (128 B)
     long long need = NSB_COL0 + (long long)P->i_max + 2 + NSB_GROUP;
     c->g.pitch = (need + 15) / 16 * 16;
-    c->g.rows = P->j_max + 2 + NSB_ROW0;
+    c->g.rows = P->j_max + 2 + NSB_ROW0 + NSB_ROWS_ABOVE;
     c->g.elems = (size_t)c->g.pitch * (size_t)c->g.rows;
     c->dx = P->a / P->i_max;                                   // main.c:72-73
     c->dy = P->b / P->j_max;

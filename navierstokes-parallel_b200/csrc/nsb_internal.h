@@ -5,7 +5,10 @@
 // COL0 = 3 puts interior column i = 1 on a 32-byte boundary (4 doubles = one "column group", the
 // unit a thread of the streaming kernels owns); pitch is a multiple of 16 doubles (128 B) and
 // leaves >= 4 padding doubles to the right of the ghost column i_max+1, so every group load is in
-// bounds.  ROW0 = 0.  This replaces the reference's row-pointer tables (`double**`, main.cu:103-120)
+// bounds.  ROW0 = 2: two pad rows lie below the ghost row j = 0 and NSB_ROWS_ABOVE = 3 above the
+// ghost row j_max+1 (zero-filled, never written), so the streaming SOR kernel, whose row window
+// reaches 3 rows beyond a chunk and which fetches rows in (even, odd) pairs, never needs a bounds
+// test on a load; in a y-slab decomposition the same rows hold the neighbour's halo.  This replaces the reference's row-pointer tables (`double**`, main.cu:103-120)
 // and its j-contiguous order, which made every warp access strided.
 #pragma once
 
@@ -15,7 +18,8 @@
 #include "../../include/nsb200.h"
 
 #define NSB_COL0 3
-#define NSB_ROW0 0
+#define NSB_ROW0 2
+#define NSB_ROWS_ABOVE 3              // pad rows above the ghost row j_max+1
 #define NSB_GROUP 4                 // doubles per column group (32 B)
 #define NSB_STRIP_GROUPS 30         // output groups per warp strip (lanes 1..30; 0 and 31 are halo)
 #define NSB_STRIP_COLS (NSB_STRIP_GROUPS * NSB_GROUP)
@@ -23,7 +27,7 @@
 struct NsbGrid {
     int ni, nj;            // global interior size (i_max, j_max)
     long long pitch;       // doubles per row
-    int rows;              // stored rows (nj + 2)
+    int rows;              // stored rows (nj + 2 + NSB_ROW0 + NSB_ROWS_ABOVE)
     size_t elems;          // pitch * rows
 };
 

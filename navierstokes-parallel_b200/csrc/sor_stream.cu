@@ -7,7 +7,7 @@
 // colour 1 (main.cu:686/694), not before the residual -- so the residual sees, next to a wall, the
 // value the wall cell had before the black sweep, as the reference does.
 //
-// Design (DESIGN.md "SOR streaming kernel"):
+// Design (DESIGN.md "SOR streaming kernel", v3):
 //   - ping-pong pressure buffers: read p_in, write p_out, so a tile never sees a half-updated
 //     neighbour and both colours are applied in one pass: algorithmic traffic 24 B per cell per
 //     iteration (p in 8 + RHS in 8 + p out 8).
@@ -15,13 +15,18 @@
 //     j.  Lane L owns 4 adjacent columns (one 32-byte sector); lanes 0 and 31 are halo lanes.
 //     x-neighbours come from warp shuffles, y-neighbours from a register window of 5 rows, so
 //     there is no block barrier anywhere.
-//   - rows are fetched by the TMA engine: one elected lane issues `cp.async.bulk` (1 KB of p and
-//     1 KB of RHS per row) into a per-warp ring of shared-memory stages, completion on an
-//     mbarrier; the ring runs SOR_STAGES rows ahead of the arithmetic, which keeps enough bytes in
-//     flight to cover HBM latency without spending registers on prefetch.
+//   - rows are fetched by the TMA engine in (even, odd) row PAIRS: one elected lane issues four
+//     `cp.async.bulk` copies (2 x 1 KB of p, 2 x 1 KB of RHS) into a per-warp ring of
+//     shared-memory stages, completion on an mbarrier.  The grids carry pad rows (NSB_ROW0,
+//     NSB_ROWS_ABOVE), so no load ever needs a bounds test.
 //   - software pipeline inside the window: when row j arrives, row j-1 gets its red update, row
 //     j-2 its black update (and is stored, two 16-byte stores = one full sector per lane), row
 //     j-3 its residual.
+//   - the step is compiled in three variants and chosen per block of 8 rows with warp-uniform
+//     branches: LEAN (interior strip, interior rows: no predicates, no ghost handling -- the
+//     variant > 90 % of the rows run), EY (rows next to the bottom / top wall or to the chunk ends)
+//     and EX+EY (first / last strip, which hold the ghost columns).  v2 ran the fully general code
+//     everywhere and spent 79 % of its instructions on predication (profiles/r1b_*).
 //   - residual: per-warp partial (fixed order), last block of the grid adds the partials in a fixed
 //     order, takes sqrt(sum/(i_max*j_max)) (main.cu:588), compares with eps*(norm_p+1.5)
 //     (main.cu:713) and raises the device-side converged flag; later launches exit at once.
@@ -35,13 +40,15 @@
 #ifndef SOR_MIN_BLOCKS
 #define SOR_MIN_BLOCKS 3
 #endif
-#ifndef SOR_STAGES
-#define SOR_STAGES 8         // rows in flight per warp (power of two, <= 8)
+#ifndef SOR_LOG_NST
+#define SOR_LOG_NST 1          // log2(row-pair stages per warp)
 #endif
-#define SOR_ROW_BYTES 1024   // 32 lanes x 32 B
-#define SOR_STAGE_BYTES (2 * SOR_ROW_BYTES)
-#define SOR_WARP_SMEM (SOR_STAGES * SOR_STAGE_BYTES)
-#define SOR_SMEM_BYTES (SOR_WARPS * SOR_WARP_SMEM + SOR_WARPS * SOR_STAGES * 8)
+#define SOR_NST (1 << SOR_LOG_NST)
+#define SOR_ROW_BYTES 1024     // 32 lanes x 32 B
+#define SOR_ROW_DBL (SOR_ROW_BYTES / 8)
+#define SOR_STAGE_BYTES (4 * SOR_ROW_BYTES)   // p even row, p odd row, RHS even row, RHS odd row
+#define SOR_WARP_SMEM (SOR_NST * SOR_STAGE_BYTES)
+#define SOR_SMEM_BYTES (SOR_WARPS * SOR_WARP_SMEM + SOR_WARPS * 2 * SOR_NST * 8)   // rings + FULL/EMPTY mbarriers
 
 struct SorStreamArgs {
     const double* __restrict__ pin;
@@ -52,6 +59,7 @@ struct SorStreamArgs {
     int chunk_rows, n_strips, n_tasks;
     int n_groups;            // pitch / 4
     int it, check;
+    unsigned int zero;       // always 0; opaque to the compiler
     SorCoef k;
     double* partials;
     SorCtl* ctl;
@@ -70,6 +78,7 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+#ifdef SOR_WAIT_CPP
     uint32_t ok;
     do {
         asm volatile(
@@ -78,6 +87,16 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
             "selp.u32 %0, 1, 0, p;\n\t}"
             : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
     } while (!ok);
+    return;
+#endif
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "DONE:\n\t}"
+        ::"r"(bar), "r"(parity) : "memory");
 }
 // global -> shared bulk copy executed by the TMA engine (UBLKCP in SASS), completes on `bar`
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
@@ -133,71 +152,119 @@ struct TaskCtx {
     int jstart, jc0, jc1;
     int nj;
     long long pitch;
-    const double* pin_row0;   // &pin[row 0][first column of the strip]
-    const double* rhs_row0;
-    double* pout_col;         // &pout[row 0][this lane's group]
-    uint32_t copy_bytes;      // bytes per row copy (1 KB, clipped at the right edge of the pitch)
-    uint32_t smem_base;       // this warp's ring
-    uint32_t bar_base;        // this warp's mbarriers
-    const double* smem_gen;   // generic pointer to this warp's ring (for LDS)
+    double* pout_row;         // &pout[row of the black update of the current step][this lane's group]
+    const double* lds_lane;   // generic pointer: this warp's ring + 4 * lane doubles
+    uint32_t bar_base;        // this warp's mbarriers (shared address): NST FULL, then NST EMPTY
     int lane;
+    uint32_t zero;            // run-time 0 (see the EMPTY-barrier arrive)
+    // producer state (warp-uniform)
+    const double* pin_next;   // first row of the next pair to fetch, first column of the strip
+    const double* rhs_next;
+    int j_next, j_limit;      // pairs whose first row is > j_limit are not fetched
+    uint32_t copy_bytes;      // bytes per row copy (1 KB, clipped at the right edge of the pitch)
+    uint32_t smem_base;       // this warp's ring (shared address)
 };
 
-// Elected lane: arm stage `st` and start the copies of row r (p) and row r (RHS) when in range.
-__device__ __forceinline__ void issue_row(const TaskCtx& t, int st, int r) {
-    const bool p_ok = (r >= 0) && (r <= t.nj + 1) && (r <= t.jc1 + 3);
-    const bool r_ok = (r >= 1) && (r <= t.nj) && (r <= t.jc1 + 2);
-    const uint32_t bar = t.bar_base + st * 8;
-    if (!p_ok) {            // nothing to fetch: complete the phase anyway so parities stay in step
-        mbar_arrive(bar);
-        return;
-    }
-    const uint32_t dst = t.smem_base + st * SOR_STAGE_BYTES;
-    mbar_expect_tx(bar, r_ok ? 2 * t.copy_bytes : t.copy_bytes);
-    bulk_g2s(dst, t.pin_row0 + (long long)r * t.pitch, t.copy_bytes, bar);
-    if (r_ok) bulk_g2s(dst + SOR_ROW_BYTES, t.rhs_row0 + (long long)r * t.pitch, t.copy_bytes, bar);
+// One elected lane arms stage `st` and starts the four copies of the next row pair.  Pairs beyond
+// the rows this task needs complete their phase without data so that the parities stay in step.
+// The producer state is kept warp-uniform (every lane advances it), and the election uses
+// elect.sync so that the compiler moves the operands to uniform registers without a lane loop.
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .b32 r;\n\t.reg .pred p;\n\t"
+        "elect.sync r|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
 }
 
-// One pipeline step with compile-time window slot S (row parity == S parity).  `step` is the step
-// number since the start of the task (step & 7 == S).
-template <bool RECIP, int S>
-__device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], const int step,
-                                         const TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, double& acc) {
+__device__ __forceinline__ void issue_pair(TaskCtx& t, int st, uint32_t empty_phase, bool wait_empty) {
+#ifdef SOR_LANE0_ISSUE
+    if (t.lane == 0) {
+#else
+    if (elect_one()) {
+#endif
+        const uint32_t bar = t.bar_base + st * 8;
+        if (wait_empty) mbar_wait(t.bar_base + (SOR_NST + st) * 8, empty_phase);
+        if (t.j_next <= t.j_limit) {
+            const uint32_t dst = t.smem_base + st * SOR_STAGE_BYTES;
+            mbar_expect_tx(bar, 4u * t.copy_bytes);
+            bulk_g2s(dst, t.pin_next, t.copy_bytes, bar);
+            bulk_g2s(dst + SOR_ROW_BYTES, t.pin_next + t.pitch, t.copy_bytes, bar);
+            bulk_g2s(dst + 2 * SOR_ROW_BYTES, t.rhs_next, t.copy_bytes, bar);
+            bulk_g2s(dst + 3 * SOR_ROW_BYTES, t.rhs_next + t.pitch, t.copy_bytes, bar);
+        } else {
+            mbar_arrive(bar);
+        }
+    }
+    t.j_next += 2;
+    t.pin_next += 2 * t.pitch;
+    t.rhs_next += 2 * t.pitch;
+}
+
+// One pipeline step with compile-time window slot S (row parity == S parity).  sb is the step
+// number of the first step of the current block of 8 (a multiple of 8); the row that arrives in
+// this step is j = jstart + sb + S.
+//   EX: the strip holds ghost / pad columns (first and last strips).
+//   EY: the block of 8 steps touches rows that need gating (walls, chunk ends).
+template <bool RECIP, bool EX, bool EY, int S>
+__device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], const int sb, TaskCtx& t,
+                                         const SorCoef& kf, const LaneGeom& lg, double& acc) {
     constexpr int sE = S & 7, sD = (S + 7) & 7, sC = (S + 6) & 7, sB = (S + 5) & 7, sA = (S + 4) & 7;
-    constexpr int st = S & (SOR_STAGES - 1);
+    constexpr int st = (S >> 1) & (SOR_NST - 1);
     constexpr int k0 = (S & 1) ? 1 : 0;     // cells updated this step: columns k0 and k0 + 2
     constexpr int k1 = k0 + 2;
     const unsigned FULL = 0xffffffffu;
-    const int j = t.jstart + step;
+    const int j = t.jstart + sb + S;
 
-    // ---- row j (p and RHS) from the ring into registers, then hand the stage back to the TMA
+    // ---- row j (p and RHS) from the ring into registers; after the odd row of a pair the stage
+    //      goes back to the TMA engine
     {
-        const bool has_row = (j >= 0) && (j <= t.nj + 1) && (j <= t.jc1 + 3);
-        mbar_wait(t.bar_base + st * 8, (uint32_t)(step / SOR_STAGES) & 1u);
-        if (has_row) {
-            const double2* q = reinterpret_cast<const double2*>(t.smem_gen + st * (SOR_STAGE_BYTES / 8)) + 2 * t.lane;
-            const double2 a = q[0], b = q[1];
-            const double2 c = q[SOR_ROW_BYTES / 16], d = q[SOR_ROW_BYTES / 16 + 1];
-            P[sE][0] = a.x; P[sE][1] = a.y; P[sE][2] = b.x; P[sE][3] = b.y;
-            R[sE][0] = c.x; R[sE][1] = c.y; R[sE][2] = d.x; R[sE][3] = d.y;
+        const uint32_t ph = ((uint32_t)(sb + S) >> (1 + SOR_LOG_NST)) & 1u;   // use count of the stage, mod 2
+        if ((S & 1) == 0) {
+            mbar_wait(t.bar_base + st * 8, ph);
+#ifdef SOR_SYNC_EACH_STEP
+            __syncwarp();
+#endif
         }
-        __syncwarp();
-        if (t.lane == 0) issue_row(t, st, j + SOR_STAGES);
+        const double2* q = reinterpret_cast<const double2*>(t.lds_lane + st * (SOR_STAGE_BYTES / 8) + (S & 1) * SOR_ROW_DBL);
+        const double2 a = q[0], b = q[1];
+        const double2 c = q[SOR_ROW_BYTES / 8], d = q[SOR_ROW_BYTES / 8 + 1];     // + 2 rows = 2 * 1024 B = 128 double2
+        P[sE][0] = a.x; P[sE][1] = a.y; P[sE][2] = b.x; P[sE][3] = b.y;
+        R[sE][0] = c.x; R[sE][1] = c.y; R[sE][2] = d.x; R[sE][3] = d.y;
+        if (S & 1) {
+            // Both rows of the pair are read: every lane releases the stage on its EMPTY barrier and
+            // the elected lane re-arms the stage only after acquiring that phase (32 arrivals).
+            // The arrive must not overtake the LDS above: neither __syncwarp() nor the arrive's
+            // release semantics kept the bulk copy from overwriting a row whose LDS was still queued
+            // (seen on B200 as sporadically wrong RHS values in the last-loaded 16 bytes).  So the
+            // barrier ADDRESS is made data-dependent on all eight LDS of the pair (this step's
+            // a, b, c, d and the previous step's, now in window slot D): `zero` is a run-time 0 the
+            // compiler cannot fold, and the arrive cannot issue before the loads have landed.
+            const int dep = (__double2hiint(a.x) ^ __double2hiint(b.x) ^ __double2hiint(c.x)) ^
+                            (__double2hiint(d.x) ^ __double2hiint(P[sD][0]) ^ __double2hiint(P[sD][2])) ^
+                            (__double2hiint(R[sD][0]) ^ __double2hiint(R[sD][2]));
+            mbar_arrive(t.bar_base + (SOR_NST + st) * 8 + ((uint32_t)dep & t.zero));
+            issue_pair(t, st, ph, true);
+        }
     }
 
     // ---- colour 0 (red) on row D = j-1; neighbours C (j-2, black cells still old) and E (j)
     {
         const int r = j - 1;
-        const bool row_in = (r >= 1) && (r <= t.nj);
+        const bool row_in = !EY || ((r >= 1) && (r <= t.nj));
         double (&X)[4] = P[sD];
-        refresh_ghost_columns(X, lg);                                   // main.cu:686
-        if (r == 1) {
+        if (EX) refresh_ghost_columns(X, lg);                           // main.cu:686
+        if (EY) {
+            if (r == 1) {
 #pragma unroll
-            for (int k = 0; k < 4; k++) P[sC][k] = X[k];                // p[i][0] = p[i][1]
-        }
-        if (r == t.nj) {
+                for (int k = 0; k < 4; k++) P[sC][k] = X[k];            // p[i][0] = p[i][1]
+            }
+            if (r == t.nj) {
 #pragma unroll
-            for (int k = 0; k < 4; k++) P[sE][k] = X[k];                // p[i][j_max+1] = p[i][j_max]
+                for (int k = 0; k < 4; k++) P[sE][k] = X[k];            // p[i][j_max+1] = p[i][j_max]
+            }
         }
         double xw = 0.0, xe = 0.0;
         if (k0 == 0) xw = __shfl_up_sync(FULL, X[3], 1);
@@ -208,23 +275,25 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
         const double e1 = (k1 == 3) ? xe : X[(k1 + 1) & 3];
         const double u0 = sor_cell<RECIP>(X[k0], e0, w0, P[sE][k0], P[sC][k0], R[sD][k0], kf);
         const double u1 = sor_cell<RECIP>(X[k1], e1, w1, P[sE][k1], P[sC][k1], R[sD][k1], kf);
-        if (row_in && lg.inner[k0]) X[k0] = u0;
-        if (row_in && lg.inner[k1]) X[k1] = u1;
+        if (row_in && (!EX || lg.inner[k0])) X[k0] = u0;
+        if (row_in && (!EX || lg.inner[k1])) X[k1] = u1;
     }
 
     // ---- colour 1 (black) on row C = j-2; neighbours B (j-3, final) and D (j-1, red done)
     {
         const int r = j - 2;
-        const bool row_in = (r >= 1) && (r <= t.nj);
+        const bool row_in = !EY || ((r >= 1) && (r <= t.nj));
         double (&X)[4] = P[sC];
-        refresh_ghost_columns(X, lg);                                   // main.cu:694
-        if (r == 1) {
+        if (EX) refresh_ghost_columns(X, lg);                           // main.cu:694
+        if (EY) {
+            if (r == 1) {
 #pragma unroll
-            for (int k = 0; k < 4; k++) P[sB][k] = X[k];
-        }
-        if (r == t.nj) {
+                for (int k = 0; k < 4; k++) P[sB][k] = X[k];
+            }
+            if (r == t.nj) {
 #pragma unroll
-            for (int k = 0; k < 4; k++) P[sD][k] = X[k];
+                for (int k = 0; k < 4; k++) P[sD][k] = X[k];
+            }
         }
         double xw = 0.0, xe = 0.0;
         if (k0 == 0) xw = __shfl_up_sync(FULL, X[3], 1);
@@ -235,14 +304,15 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
         const double e1 = (k1 == 3) ? xe : X[(k1 + 1) & 3];
         const double u0 = sor_cell<RECIP>(X[k0], e0, w0, P[sD][k0], P[sB][k0], R[sC][k0], kf);
         const double u1 = sor_cell<RECIP>(X[k1], e1, w1, P[sD][k1], P[sB][k1], R[sC][k1], kf);
-        if (row_in && lg.inner[k0]) X[k0] = u0;
-        if (row_in && lg.inner[k1]) X[k1] = u1;
+        if (row_in && (!EX || lg.inner[k0])) X[k0] = u0;
+        if (row_in && (!EX || lg.inner[k1])) X[k1] = u1;
         // row j-2 is final: store it (one full 32-byte sector per lane)
-        if (lg.owner && r >= t.jc0 && r <= t.jc1) {
-            double2* q = reinterpret_cast<double2*>(t.pout_col + (long long)r * t.pitch);
+        if (lg.owner && (!EY || (r >= t.jc0 && r <= t.jc1))) {
+            double2* q = reinterpret_cast<double2*>(t.pout_row);
             q[0] = make_double2(X[0], X[1]);
             q[1] = make_double2(X[2], X[3]);
         }
+        t.pout_row += t.pitch;
     }
 
     // ---- residual on row B = j-3 with the ghosts as they are (last refreshed before colour 1)
@@ -251,22 +321,65 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
         double (&X)[4] = P[sB];
         const double xw = __shfl_up_sync(FULL, X[3], 1);
         const double xe = __shfl_down_sync(FULL, X[0], 1);
-        if (r >= t.jc0 && r <= t.jc1) {       // warp-uniform; rows of the chunk are interior rows
+        if (!EY || (r >= t.jc0 && r <= t.jc1)) {   // warp-uniform; rows of the chunk are interior rows
             double part = 0.0;
 #pragma unroll
             for (int k = 0; k < 4; k++) {
                 const double w = (k == 0) ? xw : X[(k + 3) & 3];
                 const double e = (k == 3) ? xe : X[(k + 1) & 3];
                 const double q = sor_residual<RECIP>(X[k], e, w, P[sC][k], P[sA][k], R[sB][k], kf);
-                if (lg.inner[k]) part = fma(q, q, part);
+                if (!EX || lg.inner[k]) part = fma(q, q, part);
             }
-            if (lg.owner) acc += part;
+            acc += part;                           // non-owner lanes are discarded at the end of the task
         }
     }
 }
 
+template <bool RECIP, bool EX, bool EY>
+__device__ __forceinline__ void sor_block8(double (&P)[8][4], double (&R)[8][4], const int sb, TaskCtx& t,
+                                           const SorCoef& kf, const LaneGeom& lg, double& acc) {
+    sor_step<RECIP, EX, EY, 0>(P, R, sb, t, kf, lg, acc);
+    sor_step<RECIP, EX, EY, 1>(P, R, sb, t, kf, lg, acc);
+    sor_step<RECIP, EX, EY, 2>(P, R, sb, t, kf, lg, acc);
+    sor_step<RECIP, EX, EY, 3>(P, R, sb, t, kf, lg, acc);
+    sor_step<RECIP, EX, EY, 4>(P, R, sb, t, kf, lg, acc);
+    sor_step<RECIP, EX, EY, 5>(P, R, sb, t, kf, lg, acc);
+    sor_step<RECIP, EX, EY, 6>(P, R, sb, t, kf, lg, acc);
+    sor_step<RECIP, EX, EY, 7>(P, R, sb, t, kf, lg, acc);
+}
+
+// One task = one strip x one chunk of rows, marched bottom to top by one warp.
+template <bool RECIP, bool EX>
+__device__ __forceinline__ double sor_run_task(TaskCtx& t, const SorCoef& kf, const LaneGeom& lg) {
+    double P[8][4], R[8][4];
+#pragma unroll
+    for (int s = 0; s < 8; s++)
+#pragma unroll
+        for (int k = 0; k < 4; k++) { P[s][k] = 0.0; R[s][k] = 0.0; }
+    double acc = 0.0;
+    const int n_steps = t.jc1 + 3 - t.jstart + 1;            // rows jstart .. jc1+3
+    for (int sb = 0; sb < n_steps; sb += 8) {
+        const int jb = t.jstart + sb;                        // row arriving in the first step of the block
+        // rows touched by the block: residual jb-3 .. jb+4, stores jb-2 .. jb+5, loads jb .. jb+7
+#ifdef SOR_NO_LEAN
+        const bool clean = false;
+#else
+        const bool clean = (jb - 3 >= t.jc0) && (jb + 5 <= t.jc1) && (jb + 7 <= t.nj);
+#endif
+        if (EX) sor_block8<RECIP, true, true>(P, R, sb, t, kf, lg, acc);
+        else if (clean) sor_block8<RECIP, false, false>(P, R, sb, t, kf, lg, acc);
+        else sor_block8<RECIP, false, true>(P, R, sb, t, kf, lg, acc);
+    }
+    return lg.owner ? acc : 0.0;
+}
+
+#ifdef SOR_MAXNREG
+#define SOR_KERNEL_ATTR __maxnreg__(SOR_MAXNREG)
+#else
+#define SOR_KERNEL_ATTR __launch_bounds__(SOR_THREADS, SOR_MIN_BLOCKS)
+#endif
 template <bool RECIP>
-__global__ void __launch_bounds__(SOR_THREADS, SOR_MIN_BLOCKS) sor_stream_kernel(const SorStreamArgs a) {
+__global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ double sh[32];
     __shared__ int is_last;
@@ -280,14 +393,23 @@ __global__ void __launch_bounds__(SOR_THREADS, SOR_MIN_BLOCKS) sor_stream_kernel
         const int g = g0 + lane;                             // column group of this lane
         const int i0 = g * NSB_GROUP - NSB_COL0;             // i of column k = 0
         LaneGeom lg;
+        bool all_inner = (g < a.n_groups);
 #pragma unroll
-        for (int k = 0; k < 4; k++) lg.inner[k] = (i0 + k >= 1) && (i0 + k <= a.ni);
+        for (int k = 0; k < 4; k++) {
+            lg.inner[k] = (i0 + k >= 1) && (i0 + k <= a.ni);
+            all_inner = all_inner && lg.inner[k];
+        }
         lg.owner = (g < a.n_groups) && lane >= 1 && lane <= NSB_STRIP_GROUPS;
         lg.ghostW = (i0 + 3 == 0);
         const int kg = a.ni + 1 - i0;
         lg.kGhostE = (kg >= 0 && kg <= 3) ? kg : -1;
         lg.warpW = __any_sync(0xffffffffu, lg.ghostW);
         lg.warpE = __any_sync(0xffffffffu, lg.kGhostE >= 0);
+#ifdef SOR_FORCE_EX
+        const bool edge_strip = true;
+#else
+        const bool edge_strip = !__all_sync(0xffffffffu, all_inner);
+#endif
 
         TaskCtx t;
         t.jc0 = 1 + chunk * a.chunk_rows;
@@ -295,45 +417,38 @@ __global__ void __launch_bounds__(SOR_THREADS, SOR_MIN_BLOCKS) sor_stream_kernel
         t.jstart = t.jc0 - 3;                                // even, because chunk_rows is even
         t.nj = a.nj;
         t.pitch = a.pitch;
-        const long long coff = (long long)NSB_ROW0 * a.pitch + (long long)g0 * NSB_GROUP;
-        t.pin_row0 = a.pin + coff;
-        t.rhs_row0 = a.rhs + coff;
-        t.pout_col = a.pout + coff + (long long)lane * NSB_GROUP;
+        t.lane = lane;
+        t.zero = a.zero;
+        const long long coff = (long long)g0 * NSB_GROUP;    // first column of the strip
+        const long long row_first = (long long)(t.jstart + NSB_ROW0) * a.pitch;
+        t.pin_next = a.pin + row_first + coff;
+        t.rhs_next = a.rhs + row_first + coff;
+        t.j_next = t.jstart;
+        t.j_limit = min(t.jc1 + 3, a.nj + 3);
+        t.pout_row = a.pout + row_first - 2 * a.pitch + coff + (long long)lane * NSB_GROUP;
         const int groups_here = min(32, a.n_groups - g0);
         t.copy_bytes = (uint32_t)groups_here * 32u;
         unsigned char* ring = smem_raw + warp * SOR_WARP_SMEM;
-        t.smem_gen = reinterpret_cast<const double*>(ring);
+        t.lds_lane = reinterpret_cast<const double*>(ring) + lane * NSB_GROUP;
         t.smem_base = smem_u32(ring);
-        t.bar_base = smem_u32(smem_raw + SOR_WARPS * SOR_WARP_SMEM + warp * SOR_STAGES * 8);
-        t.lane = lane;
+        t.bar_base = smem_u32(smem_raw + SOR_WARPS * SOR_WARP_SMEM + warp * 2 * SOR_NST * 8);
 
         if (lane == 0) {
 #pragma unroll
-            for (int s = 0; s < SOR_STAGES; s++) mbar_init(t.bar_base + s * 8, 1);
+            for (int s = 0; s < SOR_NST; s++) {
+                mbar_init(t.bar_base + s * 8, 1);                    // FULL: the producer's expect_tx
+                mbar_init(t.bar_base + (SOR_NST + s) * 8, 32);       // EMPTY: every lane has read the stage
+            }
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-#pragma unroll
-            for (int s = 0; s < SOR_STAGES; s++) issue_row(t, s, t.jstart + s);
         }
         __syncwarp();
+#pragma unroll
+        for (int s = 0; s < SOR_NST; s++) issue_pair(t, s, 0u, false);
 
-        double P[8][4], R[8][4];
-#pragma unroll
-        for (int s = 0; s < 8; s++)
-#pragma unroll
-            for (int k = 0; k < 4; k++) { P[s][k] = 0.0; R[s][k] = 0.0; }
-        double acc = 0.0;
-        const int n_steps = t.jc1 + 3 - t.jstart + 1;        // rows jstart .. jc1+3
-        for (int sb = 0; sb < n_steps; sb += 8) {
-            sor_step<RECIP, 0>(P, R, sb + 0, t, a.k, lg, acc);
-            sor_step<RECIP, 1>(P, R, sb + 1, t, a.k, lg, acc);
-            sor_step<RECIP, 2>(P, R, sb + 2, t, a.k, lg, acc);
-            sor_step<RECIP, 3>(P, R, sb + 3, t, a.k, lg, acc);
-            sor_step<RECIP, 4>(P, R, sb + 4, t, a.k, lg, acc);
-            sor_step<RECIP, 5>(P, R, sb + 5, t, a.k, lg, acc);
-            sor_step<RECIP, 6>(P, R, sb + 6, t, a.k, lg, acc);
-            sor_step<RECIP, 7>(P, R, sb + 7, t, a.k, lg, acc);
-        }
+        double acc;
+        if (edge_strip) acc = sor_run_task<RECIP, true>(t, a.k, lg);
+        else acc = sor_run_task<RECIP, false>(t, a.k, lg);
         acc = warp_sum(acc);
         if (lane == 0) a.partials[task] = acc;
     }
@@ -376,7 +491,7 @@ void nsb_sor_plan(nsb_ctx* c) {
     if (c->O.sor_chunk_rows > 0) {
         best = (c->O.sor_chunk_rows + 1) & ~1;
     } else {
-        for (int rows = 16; rows <= 1024; rows += 2) {
+        for (int rows = 16; rows <= 2048; rows += 2) {
             long long chunks = (nj + rows - 1) / rows;
             long long tasks = chunks * c->n_strips;
             long long waves = (tasks + slots - 1) / slots;
@@ -397,7 +512,7 @@ cudaError_t nsb_launch_sor_stream_iter(nsb_ctx* c, int it, const double* pin, do
     a.pitch = c->g.pitch; a.ni = c->g.ni; a.nj = c->g.nj;
     a.chunk_rows = c->chunk_rows; a.n_strips = c->n_strips; a.n_tasks = c->n_partials;
     a.n_groups = (int)(c->g.pitch / NSB_GROUP);
-    a.it = it; a.check = check;
+    a.it = it; a.check = check; a.zero = 0u;
     const double dx2 = c->dx * c->dx, dy2 = c->dy * c->dy;
     a.k.om1 = 1.0 - c->P.omega;
     a.k.w = c->P.omega / (2.0 * (1.0 / dx2 + 1.0 / dy2));
