@@ -76,7 +76,7 @@ typedef struct nsb_options {
     int div_mode;        /* NSB_DIV_*                                                           */
     int sor_engine;      /* NSB_SOR_*                                                           */
     int sor_chunk_rows;  /* rows per streaming chunk (0 = auto)                                 */
-    int sor_check_batch; /* iterations queued between host looks at the convergence flag (0=auto) */
+    int sor_check_batch; /* SOR launches the host may run ahead of the device (0 = auto, 24)      */
     void* stream;        /* cudaStream_t to run on (NULL = library creates its own)              */
     int reserved[8];
 } nsb_options;

@@ -154,9 +154,15 @@ extern "C" int nsb_create(const nsb_params* P, const nsb_options* opt, nsb_ctx**
     CUC(cudaMalloc((void**)&c->d_red, sizeof(StepRed)));
     CUC(cudaMemsetAsync(c->d_ctl, 0, sizeof(SorCtl), c->stream));
     CUC(cudaMemsetAsync(c->d_red, 0, sizeof(StepRed), c->stream));
-    CUC(cudaHostAlloc((void**)&c->h_ctl, sizeof(SorCtl) * 2, cudaHostAllocDefault));
+    CUC(cudaHostAlloc((void**)&c->h_ctl, sizeof(SorCtl) * 2, cudaHostAllocMapped));
     CUC(cudaHostAlloc((void**)&c->h_red, sizeof(StepRed), cudaHostAllocDefault));
     memset(c->h_ctl, 0, sizeof(SorCtl) * 2);
+    {   // device-side control block points at its host twin
+        SorCtl init;
+        memset(&init, 0, sizeof init);
+        CUC(cudaHostGetDevicePointer((void**)&init.mirror, c->h_ctl, 0));
+        CUC(cudaMemcpyAsync(c->d_ctl, &init, sizeof init, cudaMemcpyHostToDevice, c->stream));
+    }
     memset(c->h_red, 0, sizeof(StepRed));
     c->red_valid = true;                                       // all-zero fields: maxima 0, sum p^2 0
     CUC(cudaEventCreate(&c->ev0));
@@ -301,6 +307,7 @@ static int sor_drive(nsb_ctx* c, int max_it, int check, int* iters_out, double* 
     const int engine = pick_engine(c);
     c->last_sor_engine = engine;
     CU(c, cudaEventRecord(c->ev0, c->stream));
+    c->h_ctl[0].iters = 0; c->h_ctl[0].converged = 0;          // the begin kernel publishes the same
     CU(c, nsb_launch_sor_begin(c));
     int iters = 0, converged = 0;
     if (engine == NSB_SOR_RESIDENT) {
@@ -310,35 +317,24 @@ static int sor_drive(nsb_ctx* c, int max_it, int check, int* iters_out, double* 
         iters = c->h_ctl[0].iters;
         converged = c->h_ctl[0].converged;
     } else {
-        // batch size: keep >= ~150 us of work between looks at the flag
-        int batch = c->O.sor_check_batch;
-        if (batch <= 0) {
-            double cells = (double)c->g.ni * (double)c->g.nj;
-            double est_us = cells * 24.0 / 5.0e6 + 3.0;       // ~5 TB/s effective + launch
-            batch = (int)(150.0 / est_us) + 1;
-            if (batch > 256) batch = 256;
-            if (engine == NSB_SOR_SIMPLE) batch = batch > 64 ? 64 : batch;
-        }
-        int queued = 0, nbatch = 0;
+        // The host runs ahead of the GPU by at most `depth` launches and watches the progress the
+        // closing block of every iteration publishes to pinned host memory (sor_publish).
+        const int depth = c->O.sor_check_batch > 0 ? c->O.sor_check_batch : 24;
+        int queued = 0;
         const int start = c->pcur;
+        volatile SorCtl* hv = c->h_ctl;                       // written by the device (zero-copy)
         while (queued < max_it) {
-            int n = max_it - queued;
-            if (n > batch) n = batch;
-            for (int q = 0; q < n; q++, queued++) {
-                if (engine == NSB_SOR_STREAM)
-                    CU(c, nsb_launch_sor_stream_iter(c, queued, c->pbuf[(start + queued) & 1],
-                                                     c->pbuf[(start + queued + 1) & 1], check));
-                else
-                    CU(c, nsb_launch_sor_simple_iter(c, queued, c->pbuf[start], check));
-            }
-            const int slot = nbatch & 1;
-            CU(c, cudaMemcpyAsync(&c->h_ctl[slot], c->d_ctl, sizeof(SorCtl), cudaMemcpyDeviceToHost, c->stream));
-            CU(c, cudaEventRecord(c->ev_chk[slot], c->stream));
-            nbatch++;
-            if (check && nbatch >= 2) {                       // look one batch behind the queue
-                const int look = (nbatch - 2) & 1;
-                CU(c, cudaEventSynchronize(c->ev_chk[look]));
-                if (c->h_ctl[look].converged) break;
+            if (engine == NSB_SOR_STREAM)
+                CU(c, nsb_launch_sor_stream_iter(c, queued, c->pbuf[(start + queued) & 1],
+                                                 c->pbuf[(start + queued + 1) & 1], check));
+            else
+                CU(c, nsb_launch_sor_simple_iter(c, queued, c->pbuf[start], check));
+            queued++;
+            if (check) {
+                while (!hv->converged && queued - hv->iters > depth) {
+                    if (cudaStreamQuery(c->stream) != cudaErrorNotReady) break;
+                }
+                if (hv->converged) break;
             }
         }
         CU(c, cudaStreamSynchronize(c->stream));

@@ -19,6 +19,7 @@ __global__ void sor_begin_kernel(SorCtl* ctl, const StepRed* red, double eps, lo
         ctl->iters = 0;
         ctl->converged = 0;
         ctl->ticket = 0;
+        sor_publish(ctl);
     }
 }
 
@@ -98,6 +99,7 @@ __global__ void sor_residual_kernel(const double* __restrict__ p, const double* 
             ctl->iters = it + 1;
             if (res <= ctl->thresh) ctl->converged = 1;
             ctl->ticket = 0;
+            sor_publish(ctl);
         }
     }
 }
