@@ -153,6 +153,42 @@ int nsb_output(nsb_ctx* ctx, double t, const char* prefix);
  * doubles, the column offset of i = 0 and the row offset of j = 0 */
 int nsb_device_view(nsb_ctx* ctx, int field, void** dptr, long long* pitch, int* col0, int* row0);
 
+/* ------------------------------------------------ A2. y-slab decomposition over the GPUs of one box
+ * New work (the reference is single-GPU): the domain is cut along y into `world` slabs of
+ * whole SOR chunks.  Halo rows of p travel inside the SOR sweep kernel as peer stores over NVLink,
+ * the residual / dt reductions are combined on the device in an order that does not depend on the
+ * decomposition, so 1, 2, 4 and 8 slabs give the same bits (DESIGN.md "multi-GPU").
+ *
+ * Two ways to run it:
+ *   - one process per GPU (bench.py under torchrun): nsb_create_slab on every rank, exchange the
+ *     descriptors (nsb_slab_export -> any all-gather -> nsb_slab_connect), then call nsb_step /
+ *     nsb_run / nsb_sor on every rank as if it were alone;
+ *   - one process, several GPUs (driver/main.c with NSB_GPUS=n): the nsb_group_* calls below.  Slabs
+ *     may share a device: they then run in lock step on one stream (how a 1-GPU box tests this). */
+int nsb_slab_partition(int j_max, int chunk_rows, int world, int rank, int* j_lo, int* nj,
+                       int* band0, int* nbands_global);            /* host arithmetic only */
+int nsb_create_slab(const nsb_params* params, const nsb_options* opt, int rank, int world, nsb_ctx** out);
+int nsb_slab_desc_bytes(void);
+int nsb_slab_export(const nsb_ctx* ctx, void* desc_out);
+int nsb_slab_connect(nsb_ctx* ctx, const void* descs_in_rank_order);
+int nsb_slab_info(const nsb_ctx* ctx, int* rank, int* world, int* j_lo, int* nj_local, int* chunk_rows);
+int nsb_slab_error(nsb_ctx* ctx);       /* 1 if a wait on a neighbour timed out */
+
+typedef struct nsb_group nsb_group;
+int nsb_group_create(const nsb_params* params, const nsb_options* opt, int n, const int* devices, nsb_group** out);
+void nsb_group_destroy(nsb_group* g);
+const char* nsb_group_last_error(const nsb_group* g);
+int nsb_group_size(const nsb_group* g);
+nsb_ctx* nsb_group_ctx(nsb_group* g, int k);
+int nsb_group_step(nsb_group* g, double t, nsb_step_info* info);
+int nsb_group_run(nsb_group* g, int max_steps, nsb_step_info* log, int max_log, int* steps, double* t_end);
+int nsb_group_sor(nsb_group* g, int* iters, double* res, double* norm_p);
+int nsb_group_sor_iterations(nsb_group* g, int n, double* res);
+double nsb_group_sor_seconds(const nsb_group* g);
+int nsb_group_upload(nsb_group* g, int field, const double* host, int layout);     /* whole domain */
+int nsb_group_download(nsb_group* g, int field, double* host, int layout);
+int nsb_group_get_center(nsb_group* g, double* u_c, double* v_c);
+
 /* ---------------------------------------------------------------- B. host-grid API
  * Same argument lists as the reference functions.  Grids are the reference's jagged `double**`
  * (memory.c:3-26): u has rows 0..i_max, v rows have entries 0..j_max, the rest are

@@ -115,6 +115,27 @@ ABI = {
     "nsb_max_mat": (C.c_double, [C.c_int, C.c_int, dbl_pp]),
     "nsb_timestep": (C.c_int, [C.POINTER(Params), C.c_double] + [dbl_pp] * 6 + [C.POINTER(StepInfo)]),
     "nsb_host_api_reset": (None, []),
+    # y-slab decomposition
+    "nsb_slab_partition": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, int_p, int_p, int_p, int_p]),
+    "nsb_create_slab": (C.c_int, [C.POINTER(Params), C.POINTER(Options), C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
+    "nsb_slab_desc_bytes": (C.c_int, []),
+    "nsb_slab_export": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "nsb_slab_connect": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "nsb_slab_info": (C.c_int, [C.c_void_p, int_p, int_p, int_p, int_p, int_p]),
+    "nsb_slab_error": (C.c_int, [C.c_void_p]),
+    "nsb_group_create": (C.c_int, [C.POINTER(Params), C.POINTER(Options), C.c_int, int_p, C.POINTER(C.c_void_p)]),
+    "nsb_group_destroy": (None, [C.c_void_p]),
+    "nsb_group_last_error": (C.c_char_p, [C.c_void_p]),
+    "nsb_group_size": (C.c_int, [C.c_void_p]),
+    "nsb_group_ctx": (C.c_void_p, [C.c_void_p, C.c_int]),
+    "nsb_group_step": (C.c_int, [C.c_void_p, C.c_double, C.POINTER(StepInfo)]),
+    "nsb_group_run": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(StepInfo), C.c_int, int_p, dbl_p]),
+    "nsb_group_sor": (C.c_int, [C.c_void_p, int_p, dbl_p, dbl_p]),
+    "nsb_group_sor_iterations": (C.c_int, [C.c_void_p, C.c_int, dbl_p]),
+    "nsb_group_sor_seconds": (C.c_double, [C.c_void_p]),
+    "nsb_group_upload": (C.c_int, [C.c_void_p, C.c_int, dbl_p, C.c_int]),
+    "nsb_group_download": (C.c_int, [C.c_void_p, C.c_int, dbl_p, C.c_int]),
+    "nsb_group_get_center": (C.c_int, [C.c_void_p, dbl_p, dbl_p]),
 }
 
 
@@ -290,3 +311,153 @@ class Solver:
         p, pitch, c0, r0 = C.c_void_p(), C.c_longlong(), C.c_int(), C.c_int()
         self._ck(self._L.nsb_device_view(self._h, field, C.byref(p), C.byref(pitch), C.byref(c0), C.byref(r0)))
         return p.value, pitch.value, c0.value, r0.value
+
+
+def slab_partition(j_max: int, chunk_rows: int, world: int, rank: int):
+    """Rows of slab `rank`: (j_lo, nj, band0, nbands_global).  Pure host arithmetic (no GPU needed)."""
+    a, b, c, d = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+    rc = lib().nsb_slab_partition(j_max, chunk_rows, world, rank, C.byref(a), C.byref(b), C.byref(c), C.byref(d))
+    if rc != 0:
+        raise NsbError(f"cannot cut j_max={j_max} into {world} slabs of {chunk_rows}-row bands")
+    return a.value, b.value, c.value, d.value
+
+
+def _options(device, div_mode, sor_engine, chunk_rows, check_batch, stream=0):
+    o = Options()
+    lib().nsb_default_options(C.byref(o))
+    o.device, o.div_mode, o.sor_engine = device, div_mode, sor_engine
+    o.sor_chunk_rows, o.sor_check_batch = chunk_rows, check_batch
+    o.stream = stream or None
+    return o
+
+
+class Group:
+    """y-slab decomposition driven by ONE process (`nsb_group`): slab k on devices[k].  Equal devices
+    are allowed -- the slabs then run in lock step on one stream, which is how a 1-GPU box tests it."""
+
+    def __init__(self, params: Params, devices, div_mode: int = DIV_AUTO, chunk_rows: int = 0, check_batch: int = 0):
+        self._L = lib()
+        self.params = params
+        o = _options(0, div_mode, SOR_STREAM, chunk_rows, check_batch)
+        dv = (C.c_int * len(devices))(*devices)
+        h = C.c_void_p()
+        rc = self._L.nsb_group_create(C.byref(params), C.byref(o), len(devices), dv, C.byref(h))
+        if rc != 0:
+            raise NsbError(self._L.nsb_group_last_error(None).decode())
+        self._h = h
+        self.shape = (params.i_max + 2, params.j_max + 2)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.nsb_group_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, rc, allow=()):
+        if rc != 0 and rc not in allow:
+            raise NsbError(f"nsb error {rc}: {self._L.nsb_group_last_error(self._h).decode()}")
+        return rc
+
+    def slabs(self):
+        out = []
+        for k in range(self._L.nsb_group_size(self._h)):
+            v = [C.c_int() for _ in range(5)]
+            self._L.nsb_slab_info(self._L.nsb_group_ctx(self._h, k), *[C.byref(x) for x in v])
+            out.append(dict(zip(("rank", "world", "j_lo", "nj", "chunk_rows"), (x.value for x in v))))
+        return out
+
+    def step(self, t) -> dict:
+        info = StepInfo()
+        self._ck(self._L.nsb_group_step(self._h, t, C.byref(info)))
+        return info.asdict()
+
+    def run(self, max_steps=0, max_log=100000):
+        log = (StepInfo * max_log)()
+        n, t = C.c_int(), C.c_double()
+        self._ck(self._L.nsb_group_run(self._h, max_steps, log, max_log, C.byref(n), C.byref(t)))
+        return [log[k].asdict() for k in range(min(n.value, max_log))], t.value
+
+    def SOR(self):
+        it, res, nrm = C.c_int(), C.c_double(), C.c_double()
+        rc = self._L.nsb_group_sor(self._h, C.byref(it), C.byref(res), C.byref(nrm))
+        if rc < 0 and rc != NOT_CONVERGED:
+            self._ck(rc)
+        return rc, it.value, res.value, nrm.value
+
+    def sor_iterations(self, n):
+        res = C.c_double()
+        self._ck(self._L.nsb_group_sor_iterations(self._h, n, C.byref(res)))
+        return res.value
+
+    def sor_seconds(self):
+        return self._L.nsb_group_sor_seconds(self._h)
+
+    def center(self):
+        a, b = C.c_double(), C.c_double()
+        self._ck(self._L.nsb_group_get_center(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def upload(self, field, a: np.ndarray, layout=LAYOUT_REF):
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        assert a.size == self.shape[0] * self.shape[1]
+        self._ck(self._L.nsb_group_upload(self._h, field, a.ctypes.data_as(dbl_p), layout))
+
+    def download(self, field, layout=LAYOUT_REF) -> np.ndarray:
+        shape = self.shape if layout == LAYOUT_REF else self.shape[::-1]
+        out = np.empty(shape, dtype=np.float64)
+        self._ck(self._L.nsb_group_download(self._h, field, out.ctypes.data_as(dbl_p), layout))
+        return out
+
+
+class SlabSolver(Solver):
+    """One slab per PROCESS (one process per GPU, e.g. under torchrun): creates the slab of `rank`,
+    exchanges the 256-byte descriptors through `all_gather` (a callable bytes -> list of bytes in rank
+    order, e.g. built on torch.distributed) and wires the peers over CUDA IPC.  After that every rank
+    calls step() / run() / SOR() as if it were alone; halos and reductions travel inside the kernels."""
+
+    def __init__(self, params: Params, rank: int, world: int, all_gather, device: int = 0, div_mode: int = DIV_AUTO,
+                 chunk_rows: int = 0, check_batch: int = 0):
+        self._L = lib()
+        self.params = params
+        o = _options(device, div_mode, SOR_STREAM, chunk_rows, check_batch)
+        h = C.c_void_p()
+        rc = self._L.nsb_create_slab(C.byref(params), C.byref(o), rank, world, C.byref(h))
+        if rc != 0:
+            raise NsbError(self._L.nsb_last_error(None).decode())
+        self._h = h
+        n = self._L.nsb_slab_desc_bytes()
+        mine = C.create_string_buffer(n)
+        self._ck(self._L.nsb_slab_export(self._h, mine))
+        blobs = all_gather(mine.raw)
+        assert len(blobs) == world and all(len(b) == n for b in blobs)
+        self._ck(self._L.nsb_slab_connect(self._h, C.create_string_buffer(b"".join(blobs), n * world)))
+        v = [C.c_int() for _ in range(5)]
+        self._L.nsb_slab_info(self._h, *[C.byref(x) for x in v])
+        self.rank, self.world, self.j_lo, self.nj, self.chunk_rows = (x.value for x in v)
+        self.shape = (params.i_max + 2, self.nj + 2)          # local rows 0 .. nj+1
+
+
+def torch_all_gather(group=None):
+    """all_gather callable for SlabSolver on top of torch.distributed (any backend)."""
+    import torch
+    import torch.distributed as dist
+
+    def gather(blob: bytes):
+        world = dist.get_world_size(group)
+        dev = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
+        t = torch.frombuffer(bytearray(blob), dtype=torch.uint8).to(dev)
+        out = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(out, t, group=group)
+        return [bytes(x.cpu().numpy().tobytes()) for x in out]
+    return gather

@@ -6,17 +6,20 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <unistd.h>
+
 #include "nsb_internal.h"
 
 static char g_create_err[512] = "";
 
-static int fail(nsb_ctx* c, int code, const char* fmt, ...) {
+int nsb_fail(nsb_ctx* c, int code, const char* fmt, ...) {
     va_list ap;
     va_start(ap, fmt);
     vsnprintf(c ? c->err : g_create_err, 512, fmt, ap);
     va_end(ap);
     return code;
 }
+#define fail nsb_fail
 
 #define CU(c, call)                                                                                \
     do {                                                                                           \
@@ -78,8 +81,10 @@ extern "C" void nsb_destroy(nsb_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
-    double* bufs[] = {c->u, c->v, c->F, c->G, c->rhs, c->pbuf[0], c->pbuf[1], c->scratch,
-                      c->d_partials, c->d_red_partials};
+    for (int r = 0; r < c->world && r < NSB_MAX_RANKS; r++)
+        if (r != c->rank && c->peer[r].mapped_ipc && c->peer[r].base) cudaIpcCloseMemHandle(c->peer[r].base);
+    if (c->arena) cudaFree(c->arena);
+    double* bufs[] = {c->d_partials, c->d_red_partials, c->d_bandvals};
     for (double* b : bufs) if (b) cudaFree(b);
     if (c->d_ctl) cudaFree(c->d_ctl);
     if (c->d_red) cudaFree(c->d_red);
@@ -93,15 +98,40 @@ extern "C" void nsb_destroy(nsb_ctx* c) {
     free(c);
 }
 
-extern "C" int nsb_create(const nsb_params* P, const nsb_options* opt, nsb_ctx** out) {
+// Rows of rank `rank` out of `world`: whole bands (SOR chunks of `chunk_rows` rows), the first
+// (nbands % world) ranks get one band more.  Pure host arithmetic (also used by the CPU tests).
+extern "C" int nsb_slab_partition(int j_max, int chunk_rows, int world, int rank, int* j_lo, int* nj,
+                                  int* band0, int* nbands_global) {
+    if (j_max < 1 || chunk_rows < 2 || (chunk_rows & 1) || world < 1 || rank < 0 || rank >= world) return NSB_ERR_ARG;
+    const int nb = (j_max + chunk_rows - 1) / chunk_rows;
+    if (nb < world) return NSB_ERR_ARG;
+    const int base = nb / world, rem = nb % world;
+    const int b0 = rank * base + (rank < rem ? rank : rem);
+    const int nbr = base + (rank < rem ? 1 : 0);
+    const int lo = b0 * chunk_rows;
+    int hi = (b0 + nbr) * chunk_rows;
+    if (hi > j_max) hi = j_max;
+    if (j_lo) *j_lo = lo;
+    if (nj) *nj = hi - lo;
+    if (band0) *band0 = b0;
+    if (nbands_global) *nbands_global = nb;
+    return NSB_OK;
+}
+
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+int nsb_create_slab_internal(const nsb_params* P, const nsb_options* opt, int rank, int world, nsb_ctx** out) {
     if (!P || !out) return fail(NULL, NSB_ERR_ARG, "nsb_create: null argument");
     *out = NULL;
     if (P->i_max < 1 || P->j_max < 1) return fail(NULL, NSB_ERR_ARG, "i_max and j_max must be >= 1");
+    if (world < 1 || world > NSB_MAX_RANKS || rank < 0 || rank >= world)
+        return fail(NULL, NSB_ERR_ARG, "bad rank %d / world %d (at most %d slabs)", rank, world, NSB_MAX_RANKS);
     nsb_ctx* c = (nsb_ctx*)calloc(1, sizeof(nsb_ctx));
     if (!c) return fail(NULL, NSB_ERR_ARG, "out of host memory");
     c->P = *P;
     if (opt) c->O = *opt; else nsb_default_options(&c->O);
     c->device = c->O.device;
+    c->rank = rank; c->world = world; c->J = P->j_max;
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev < 1) {
@@ -126,30 +156,88 @@ extern "C" int nsb_create(const nsb_params* P, const nsb_options* opt, nsb_ctx**
     if (c->O.stream) { c->stream = (cudaStream_t)c->O.stream; c->own_stream = false; }
     else { CUC(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)); c->own_stream = true; }
 
-    c->g.ni = P->i_max; c->g.nj = P->j_max;
-    // pitch: COL0 + (ni+2) columns + one spare group, rounded up to 16 doubles (128 B)
-    long long need = NSB_COL0 + (long long)P->i_max + 2 + NSB_GROUP;
-    c->g.pitch = (need + 15) / 16 * 16;
-    c->g.rows = P->j_max + 2 + NSB_ROW0 + NSB_ROWS_ABOVE;
-    c->g.elems = (size_t)c->g.pitch * (size_t)c->g.rows;
-    c->dx = P->a / P->i_max;                                   // main.c:72-73
+    c->dx = P->a / P->i_max;                                   // main.c:72-73 (global sizes)
     c->dy = P->b / P->j_max;
     c->recip_exact = is_pow2(c->dx * c->dx) && is_pow2(c->dy * c->dy);
     c->use_recip = (c->O.div_mode == NSB_DIV_RECIP) || (c->O.div_mode == NSB_DIV_AUTO && c->recip_exact);
 
-    const size_t bytes = c->g.elems * sizeof(double);
-    double** grids[] = {&c->u, &c->v, &c->F, &c->G, &c->rhs, &c->pbuf[0], &c->pbuf[1], &c->scratch};
-    for (double** gp : grids) {
-        CUC(cudaMalloc((void**)gp, bytes));
-        CUC(cudaMemsetAsync(*gp, 0, bytes, c->stream));        // calloc semantics, memory.c:3-26
+    // ---- rows of this slab
+    c->g.ni = P->i_max;
+    if (world == 1) {
+        c->g.nj = P->j_max; c->j_lo = 0;
+    } else {
+        // the chunk height is part of the decomposition: fixed before the rows are dealt out
+        int ch = c->O.sor_chunk_rows > 0 ? ((c->O.sor_chunk_rows + 1) & ~1) : 120;
+        if (ch < 16) ch = 16;
+        c->O.sor_chunk_rows = ch;
+        int nj = 0;
+        if (nsb_slab_partition(P->j_max, ch, world, rank, &c->j_lo, &nj, &c->band0, &c->nbands_global) != NSB_OK) {
+            fail(NULL, NSB_ERR_ARG, "j_max = %d gives fewer than %d bands of %d rows: too many slabs", P->j_max, world, ch);
+            nsb_destroy(c);
+            return NSB_ERR_ARG;
+        }
+        c->g.nj = nj;
     }
+    c->wall_bottom = (rank == 0);
+    c->wall_top = (rank == world - 1);
+    // pitch: COL0 + (ni+2) columns + one spare group, rounded up to 16 doubles (128 B)
+    long long need = NSB_COL0 + (long long)P->i_max + 2 + NSB_GROUP;
+    c->g.pitch = (need + 15) / 16 * 16;
+    c->g.rows = c->g.nj + 2 + NSB_ROW0 + NSB_ROWS_ABOVE;
+    c->g.elems = (size_t)c->g.pitch * (size_t)c->g.rows;
+
+    nsb_sor_plan(c);                                           // chunk_rows, n_strips, n_chunks, n_partials
+    if (world == 1) { c->band0 = 0; c->nbands_global = c->n_chunks; }
+
+    // ---- one arena: 8 grids, the sync block, the SOR halo flags, the reduction gather buffer
+    const size_t gbytes = align_up(c->g.elems * sizeof(double), 256);
+    size_t off = 0;
+    NsbSlabDesc& d = c->desc;
+    memset(&d, 0, sizeof d);
+    d.off_u = off; off += gbytes;
+    d.off_v = off; off += gbytes;
+    d.off_G = off; off += gbytes;
+    d.off_p[0] = off; off += gbytes;
+    d.off_p[1] = off; off += gbytes;
+    const size_t off_F = off; off += gbytes;
+    d.off_rhs = off; off += gbytes;
+    const size_t off_scratch = off; off += gbytes;
+    d.off_sync = off; off += align_up(sizeof(SlabSync), 256);
+    d.off_sorflag = off; off += align_up((size_t)2 * c->n_strips * sizeof(unsigned long long), 256);
+    d.off_gband = off; off += align_up((size_t)2 * NSB_RED_Q * c->nbands_global * sizeof(double), 256);
+    c->arena_bytes = off;
+    CUC(cudaMalloc((void**)&c->arena, c->arena_bytes));
+    CUC(cudaMemsetAsync(c->arena, 0, c->arena_bytes, c->stream));   // calloc semantics, memory.c:3-26
+    c->u = (double*)(c->arena + d.off_u); c->v = (double*)(c->arena + d.off_v);
+    c->G = (double*)(c->arena + d.off_G); c->F = (double*)(c->arena + off_F);
+    c->rhs = (double*)(c->arena + d.off_rhs); c->scratch = (double*)(c->arena + off_scratch);
+    c->pbuf[0] = (double*)(c->arena + d.off_p[0]); c->pbuf[1] = (double*)(c->arena + d.off_p[1]);
+    c->d_sync = (SlabSync*)(c->arena + d.off_sync);
+    c->d_sorflag = (unsigned long long*)(c->arena + d.off_sorflag);
+    c->d_gband = (double*)(c->arena + d.off_gband);
     c->pcur = 0;
-    nsb_sor_plan(c);
+    d.base = (unsigned long long)(uintptr_t)c->arena;
+    d.pid = (long long)getpid();
+    d.device = c->device; d.rank = rank; d.world = world; d.nj = c->g.nj; d.j_lo = c->j_lo;
+    d.n_strips = c->n_strips; d.nbands_global = c->nbands_global; d.band0 = c->band0;
+    d.pitch = c->g.pitch; d.arena_bytes = (long long)c->arena_bytes;
+    if (world > 1) {
+        cudaIpcMemHandle_t h;
+        CUC(cudaIpcGetMemHandle(&h, c->arena));
+        memcpy(d.ipc, &h, sizeof h);
+    }
+    // this rank seen as a peer of itself
+    SlabPeer& me = c->peer[rank];
+    me.base = c->arena; me.u = c->u; me.v = c->v; me.G = c->G; me.rhs = c->rhs; me.p[0] = c->pbuf[0]; me.p[1] = c->pbuf[1];
+    me.sync = c->d_sync; me.sorflag = c->d_sorflag; me.gband = c->d_gband; me.nj = c->g.nj; me.mapped_ipc = false;
+    c->connected = (world == 1);
+
     int np = c->n_partials;
-    if (np < 8 * P->j_max + 64) np = 8 * P->j_max + 64;
+    if (np < 8 * c->g.nj + 64) np = 8 * c->g.nj + 64;
     CUC(cudaMalloc((void**)&c->d_partials, (size_t)np * sizeof(double)));
-    c->n_red_partials = 3 * 4 * P->j_max + 64;
+    c->n_red_partials = 3 * 4 * c->g.nj + 64;
     CUC(cudaMalloc((void**)&c->d_red_partials, (size_t)c->n_red_partials * sizeof(double)));
+    CUC(cudaMalloc((void**)&c->d_bandvals, (size_t)NSB_RED_Q * (c->n_chunks + 1) * sizeof(double)));
     CUC(cudaMalloc((void**)&c->d_ctl, sizeof(SorCtl)));
     CUC(cudaMalloc((void**)&c->d_red, sizeof(StepRed)));
     CUC(cudaMemsetAsync(c->d_ctl, 0, sizeof(SorCtl), c->stream));
@@ -175,6 +263,10 @@ extern "C" int nsb_create(const nsb_params* P, const nsb_options* opt, nsb_ctx**
     return NSB_OK;
 }
 
+extern "C" int nsb_create(const nsb_params* P, const nsb_options* opt, nsb_ctx** out) {
+    return nsb_create_slab_internal(P, opt, 0, 1, out);
+}
+
 extern "C" int nsb_get_params(const nsb_ctx* c, nsb_params* out) {
     if (!c || !out) return NSB_ERR_ARG;
     *out = c->P;
@@ -185,251 +277,53 @@ extern "C" void* nsb_stream(const nsb_ctx* c) { return c ? (void*)c->stream : NU
 
 extern "C" double nsb_sor_seconds(const nsb_ctx* c) { return c ? c->sor_seconds : 0.0; }
 
-// ------------------------------------------------------------------ dt, gamma
-static int refresh_reductions(nsb_ctx* c) {
-    if (c->red_valid) return NSB_OK;
-    CU(c, nsb_launch_reduce_uvp(c));
-    CU(c, cudaMemcpyAsync(c->h_red, c->d_red, sizeof(StepRed), cudaMemcpyDeviceToHost, c->stream));
-    CU(c, cudaStreamSynchronize(c->stream));
-    c->red_valid = true;
-    return NSB_OK;
-}
-
-extern "C" int nsb_max_uv(nsb_ctx* c, double* u_max, double* v_max) {
-    if (!c) return NSB_ERR_ARG;
+// u and v at (i, local row l)
+int nsb_get_value(nsb_ctx* c, int i, int l, double* u_c, double* v_c) {
     CU(c, cudaSetDevice(c->device));
-    int r = refresh_reductions(c);
-    if (r) return r;
-    if (u_max) *u_max = c->h_red->u_max;
-    if (v_max) *v_max = c->h_red->v_max;
-    return NSB_OK;
-}
-
-// main.c:91-92 with n_min (io.c:141-161): min starts from the first argument, strict `>` compares.
-extern "C" int nsb_dt_gamma(const nsb_ctx* c, double u_max, double v_max, double* dt, double* gamma) {
-    if (!c) return NSB_ERR_ARG;
-    const double dx = c->dx, dy = c->dy;
-    double m = c->P.Re / 2.0 / (1.0 / dx / dx + 1.0 / dy / dy);
-    const double cu = dx / fabs(u_max), cv = dy / fabs(v_max);
-    if (m > cu) m = cu;
-    if (m > cv) m = cv;
-    const double d = c->P.tau * m;
-    if (dt) *dt = d;
-    if (gamma) *gamma = fmax(u_max * d / dx, v_max * d / dy);
-    return NSB_OK;
-}
-
-// ------------------------------------------------------------------ boundary conditions
-extern "C" int nsb_set_inflow(nsb_ctx* c, int side, double u_fix, double v_fix) {
-    if (!c) return NSB_ERR_ARG;
-    if (side < 0 || side > 3) return -1;                       // boundaries.c:34-35
-    CU(c, cudaSetDevice(c->device));
-    CU(c, nsb_launch_set_inflow(c, side, u_fix, v_fix));
-    c->red_valid = false;
-    return NSB_OK;
-}
-
-extern "C" int nsb_set_noslip(nsb_ctx* c, int side) { return nsb_set_inflow(c, side, 0.0, 0.0); }
-
-static int apply_bc_keep_reductions(nsb_ctx* c, double t) {
-    double lid;
-    if (c->P.problem == 1) lid = 1.0;                          // main.c:95-99
-    else if (c->P.problem == 2) lid = sin(c->P.f * t);         // main.c:100-104
-    else return fail(c, NSB_ERR_PROBLEM, "Unknown probem type (see parameters.txt).");
-    CU(c, nsb_launch_set_inflow(c, NSB_LEFT, 0.0, 0.0));
-    CU(c, nsb_launch_set_inflow(c, NSB_RIGHT, 0.0, 0.0));
-    CU(c, nsb_launch_set_inflow(c, NSB_BOTTOM, 0.0, 0.0));
-    CU(c, nsb_launch_set_inflow(c, NSB_TOP, lid, 0.0));
-    return NSB_OK;
-}
-
-extern "C" int nsb_apply_bc(nsb_ctx* c, double t) {
-    if (!c) return NSB_ERR_ARG;
-    CU(c, cudaSetDevice(c->device));
-    int r = apply_bc_keep_reductions(c, t);
-    c->red_valid = false;
-    return r;
-}
-
-// ------------------------------------------------------------------ F, G, RHS, update
-extern "C" int nsb_fg(nsb_ctx* c, double dt, double gamma) {
-    if (!c) return NSB_ERR_ARG;
-    CU(c, cudaSetDevice(c->device));
-    CU(c, nsb_launch_fg(c, dt, gamma));
-    return NSB_OK;
-}
-
-extern "C" int nsb_rhs(nsb_ctx* c, double dt) {
-    if (!c) return NSB_ERR_ARG;
-    CU(c, cudaSetDevice(c->device));
-    CU(c, nsb_launch_rhs(c, dt));
-    return NSB_OK;
-}
-
-extern "C" int nsb_fg_rhs(nsb_ctx* c, double dt, double gamma) {
-    if (!c) return NSB_ERR_ARG;
-    CU(c, cudaSetDevice(c->device));
-    CU(c, nsb_launch_fg_rhs(c, dt, gamma));
-    return NSB_OK;
-}
-
-extern "C" int nsb_update_uv(nsb_ctx* c, double dt) {
-    if (!c) return NSB_ERR_ARG;
-    CU(c, cudaSetDevice(c->device));
-    CU(c, nsb_launch_update_uv(c, dt));
-    CU(c, cudaMemcpyAsync(c->h_red, c->d_red, sizeof(StepRed), cudaMemcpyDeviceToHost, c->stream));
-    CU(c, cudaStreamSynchronize(c->stream));
-    c->red_valid = true;
-    return NSB_OK;
-}
-
-// ------------------------------------------------------------------ SOR drive loop
-// The reference's host loop (main.cu:684-719) synchronises six times and copies the residual to
-// the host in every iteration.  Here the convergence test runs on the device (the iteration that
-// meets the threshold raises a flag; iterations already queued behind it return immediately), and
-// the host only looks at the control block once per batch, always one batch behind the queue so
-// the GPU never idles.
-static int pick_engine(const nsb_ctx* c) {
-    int e = c->O.sor_engine;
-    if (e == NSB_SOR_AUTO) {
-        const char* env = getenv("NSB_SOR_ENGINE");
-        if (env) e = atoi(env);
-    }
-    if (e == NSB_SOR_AUTO) e = nsb_sor_resident_supported(c) ? NSB_SOR_RESIDENT : NSB_SOR_STREAM;
-    if (e == NSB_SOR_RESIDENT && !nsb_sor_resident_supported(c)) e = NSB_SOR_STREAM;
-    return e;
-}
-
-static int sor_drive(nsb_ctx* c, int max_it, int check, int* iters_out, double* res_out, double* normp_out,
-                     int* converged_out) {
-    int r = refresh_reductions(c);                             // sum p^2 for norm_p (main.cu:675)
-    if (r) return r;
-    const int engine = pick_engine(c);
-    c->last_sor_engine = engine;
-    CU(c, cudaEventRecord(c->ev0, c->stream));
-    c->h_ctl[0].iters = 0; c->h_ctl[0].converged = 0;          // the begin kernel publishes the same
-    CU(c, nsb_launch_sor_begin(c));
-    int iters = 0, converged = 0;
-    if (engine == NSB_SOR_RESIDENT) {
-        CU(c, nsb_launch_sor_resident(c, max_it, check));
-        CU(c, cudaMemcpyAsync(c->h_ctl, c->d_ctl, sizeof(SorCtl), cudaMemcpyDeviceToHost, c->stream));
-        CU(c, cudaStreamSynchronize(c->stream));
-        iters = c->h_ctl[0].iters;
-        converged = c->h_ctl[0].converged;
-    } else {
-        // The host runs ahead of the GPU by at most `depth` launches and watches the progress the
-        // closing block of every iteration publishes to pinned host memory (sor_publish).
-        const int depth = c->O.sor_check_batch > 0 ? c->O.sor_check_batch : 24;
-        int queued = 0;
-        const int start = c->pcur;
-        volatile SorCtl* hv = c->h_ctl;                       // written by the device (zero-copy)
-        while (queued < max_it) {
-            if (engine == NSB_SOR_STREAM)
-                CU(c, nsb_launch_sor_stream_iter(c, queued, c->pbuf[(start + queued) & 1],
-                                                 c->pbuf[(start + queued + 1) & 1], check));
-            else
-                CU(c, nsb_launch_sor_simple_iter(c, queued, c->pbuf[start], check));
-            queued++;
-            if (check) {
-                while (!hv->converged && queued - hv->iters > depth) {
-                    if (cudaStreamQuery(c->stream) != cudaErrorNotReady) break;
-                }
-                if (hv->converged) break;
-            }
-        }
-        CU(c, cudaStreamSynchronize(c->stream));
-        // the flag may have been raised inside the last batch(es) we did not look at
-        CU(c, cudaMemcpy(&c->h_ctl[0], c->d_ctl, sizeof(SorCtl), cudaMemcpyDeviceToHost));
-        iters = c->h_ctl[0].iters;
-        converged = c->h_ctl[0].converged;
-        if (engine == NSB_SOR_STREAM) {
-            c->pcur = (start + iters) & 1;
-            if (iters > 0) CU(c, nsb_launch_sor_finish_ghosts(c, c->pbuf[c->pcur], c->pbuf[c->pcur ^ 1]));
-        }
-    }
-    CU(c, cudaEventRecord(c->ev1, c->stream));
-    CU(c, cudaEventSynchronize(c->ev1));
-    float ms = 0.f;
-    CU(c, cudaEventElapsedTime(&ms, c->ev0, c->ev1));
-    c->sor_seconds += (double)ms * 1e-3;
-    if (iters_out) *iters_out = iters;
-    if (res_out) *res_out = c->h_ctl[0].res;
-    if (normp_out) *normp_out = c->h_ctl[0].norm_p;
-    if (converged_out) *converged_out = converged;
-    return NSB_OK;
-}
-
-extern "C" int nsb_sor(nsb_ctx* c, int* iters, double* res, double* norm_p) {
-    if (!c) return NSB_ERR_ARG;
-    CU(c, cudaSetDevice(c->device));
-    int it = 0, conv = 0;
-    int r = sor_drive(c, c->P.max_it, 1, &it, res, norm_p, &conv);
-    if (r) return r;
-    if (iters) *iters = it;
-    return conv ? it : NSB_NOT_CONVERGED;                      // main.cu:717 / :725
-}
-
-extern "C" int nsb_sor_iterations(nsb_ctx* c, int n, double* res) {
-    if (!c) return NSB_ERR_ARG;
-    CU(c, cudaSetDevice(c->device));
-    int it = 0;
-    int r = sor_drive(c, n, 0, &it, res, NULL, NULL);
-    c->red_valid = false;                                      // p changed outside a time step
-    return r;
-}
-
-// ------------------------------------------------------------------ whole step / whole run
-extern "C" int nsb_step(nsb_ctx* c, double t, nsb_step_info* info) {
-    if (!c) return NSB_ERR_ARG;
-    CU(c, cudaSetDevice(c->device));
-    double u_max, v_max, dt, gamma;
-    int r = nsb_max_uv(c, &u_max, &v_max);                     // main.c:89-90
-    if (r) return r;
-    nsb_dt_gamma(c, u_max, v_max, &dt, &gamma);                // main.c:91-92
-    r = apply_bc_keep_reductions(c, t);                        // main.c:95-108
-    if (r) return r;
-    CU(c, nsb_launch_fg_rhs(c, dt, gamma));                    // main.c:112-120
-    int iters = 0, conv = 0;
-    double res = 0.0, norm_p = 0.0;
-    r = sor_drive(c, c->P.max_it, 1, &iters, &res, &norm_p, &conv);   // main.c:123
-    if (r) return r;
-    r = nsb_update_uv(c, dt);                                  // main.c:131-136
-    if (r) return r;
-    if (info) {
-        info->t = t; info->dt = dt; info->gamma = gamma; info->u_max = u_max; info->v_max = v_max;
-        info->norm_p = norm_p; info->res = res; info->sor_iters = iters;
-        info->sor_ret = conv ? iters : NSB_NOT_CONVERGED;
-    }
-    return NSB_OK;
-}
-
-extern "C" int nsb_run(nsb_ctx* c, int max_steps, nsb_step_info* log, int max_log, int* steps, double* t_end) {
-    if (!c) return NSB_ERR_ARG;
-    double t = 0.0;
-    int n = 0;
-    while (t < c->P.T && (max_steps <= 0 || n < max_steps)) {  // main.c:86
-        nsb_step_info info;
-        int r = nsb_step(c, t, &info);
-        if (r) return r;
-        if (log && n < max_log) log[n] = info;
-        t += info.dt;                                          // main.c:145
-        n++;
-    }
-    if (steps) *steps = n;
-    if (t_end) *t_end = t;
-    return NSB_OK;
-}
-
-extern "C" int nsb_get_center(nsb_ctx* c, double* u_c, double* v_c) {
-    if (!c) return NSB_ERR_ARG;
-    CU(c, cudaSetDevice(c->device));
-    const size_t o = nsb_index(c->g, c->P.i_max / 2, c->P.j_max / 2);   // main.c:148-149
+    const size_t o = nsb_index(c->g, i, l);
     double uv[2];
     CU(c, cudaMemcpyAsync(&uv[0], c->u + o, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaMemcpyAsync(&uv[1], c->v + o, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
     if (u_c) *u_c = uv[0];
     if (v_c) *v_c = uv[1];
+    return NSB_OK;
+}
+
+// main.c:148-149.  On a slab that does not hold the global row j_max/2 this is NSB_ERR_ARG
+// (nsb_group_get_center / the python host pick the right rank).
+extern "C" int nsb_get_center(nsb_ctx* c, double* u_c, double* v_c) {
+    if (!c) return NSB_ERR_ARG;
+    const int l = c->J / 2 - c->j_lo;
+    if (!((l >= 1 && l <= c->g.nj) || (l == 0 && c->wall_bottom)))
+        return fail(c, NSB_ERR_ARG, "global row %d is not on slab %d", c->J / 2, c->rank);
+    return nsb_get_value(c, c->P.i_max / 2, l, u_c, v_c);
+}
+
+// `nrows` rows starting at local row l0 between the slab and a dense x-fastest host block
+// ((i_max+2) doubles per row).  up != 0: host -> HBM.
+int nsb_xfer_rows(nsb_ctx* c, int field, double* host, int l0, int nrows, int up) {
+    CU(c, cudaSetDevice(c->device));
+    double* dev = NULL;
+    switch (field) {
+        case NSB_U: dev = c->u; break;
+        case NSB_V: dev = c->v; break;
+        case NSB_P: dev = c->pbuf[c->pcur]; break;
+        case NSB_F: dev = c->F; break;
+        case NSB_G: dev = c->G; break;
+        case NSB_RHS: dev = c->rhs; break;
+    }
+    if (!dev) return fail(c, NSB_ERR_ARG, "unknown field %d", field);
+    if (nrows <= 0) return NSB_OK;
+    const size_t nx = (size_t)c->g.ni + 2;
+    double* d = dev + (long long)(l0 + NSB_ROW0) * c->g.pitch + NSB_COL0;
+    if (up)
+        CU(c, cudaMemcpy2DAsync(d, c->g.pitch * sizeof(double), host, nx * sizeof(double), nx * sizeof(double),
+                                (size_t)nrows, cudaMemcpyHostToDevice, c->stream));
+    else
+        CU(c, cudaMemcpy2DAsync(host, nx * sizeof(double), d, c->g.pitch * sizeof(double), nx * sizeof(double),
+                                (size_t)nrows, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
     return NSB_OK;
 }
 

@@ -10,8 +10,11 @@
 // a warp touches 256 contiguous bytes per array (the reference maps threadIdx.x to the strided
 // index).  Arithmetic order is the reference's, evaluated with non-contracting
 // intrinsics (nsb_math.cuh), so F, G, RHS, u, v are bit-identical to the CPU build.
+#include <string.h>
+
 #include "nsb_internal.h"
 #include "nsb_math.cuh"
+#include "slab.cuh"
 
 #define MB_X 128
 #define MB_Y 2
@@ -73,6 +76,8 @@ __global__ void set_inflow_kernel(double* u, double* v, long long pitch, int ni,
 }
 
 cudaError_t nsb_launch_set_inflow(nsb_ctx* c, int side, double u_fix, double v_fix) {
+    if (side == NSB_TOP && !c->wall_top) return cudaSuccess;          // the lid belongs to the last slab
+    if (side == NSB_BOTTOM && !c->wall_bottom) return cudaSuccess;
     const int n = (side == NSB_TOP || side == NSB_BOTTOM) ? c->g.ni : c->g.nj;
     set_inflow_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(c->u, c->v, c->g.pitch, c->g.ni, c->g.nj,
                                                               side, u_fix, v_fix);
@@ -142,20 +147,21 @@ __device__ __forceinline__ double g_cell(const double* __restrict__ U, const dou
 template <bool RECIP>
 __global__ void __launch_bounds__(MB_X* MB_Y) fg_kernel(const double* __restrict__ u, const double* __restrict__ v,
                                                          double* __restrict__ F, double* __restrict__ G,
-                                                         long long pitch, int ni, int nj, MomCoef m) {
+                                                         long long pitch, int ni, int nj, int g_hi, MomCoef m) {
     const int i = blockIdx.x * MB_X + threadIdx.x + 1;
     const int j = blockIdx.y * MB_Y + threadIdx.y + 1;
     if (i > ni || j > nj) return;
     const long long o = (long long)(j + NSB_ROW0) * pitch + NSB_COL0 + i;
     if (i <= ni - 1) F[o] = f_cell<RECIP>(u, v, o, pitch, m);
-    if (j <= nj - 1) G[o] = g_cell<RECIP>(u, v, o, pitch, m);
+    if (j <= g_hi) G[o] = g_cell<RECIP>(u, v, o, pitch, m);       // global j <= j_max-1 (integration.c:84)
 }
 
 cudaError_t nsb_launch_fg(nsb_ctx* c, double dt, double gamma) {
     MomCoef m = make_mom(c, dt, gamma);
     dim3 b(MB_X, MB_Y), g((c->g.ni + MB_X - 1) / MB_X, (c->g.nj + MB_Y - 1) / MB_Y);
-    if (c->use_recip) fg_kernel<true><<<g, b, 0, c->stream>>>(c->u, c->v, c->F, c->G, c->g.pitch, c->g.ni, c->g.nj, m);
-    else fg_kernel<false><<<g, b, 0, c->stream>>>(c->u, c->v, c->F, c->G, c->g.pitch, c->g.ni, c->g.nj, m);
+    const int g_hi = c->wall_top ? c->g.nj - 1 : c->g.nj;
+    if (c->use_recip) fg_kernel<true><<<g, b, 0, c->stream>>>(c->u, c->v, c->F, c->G, c->g.pitch, c->g.ni, c->g.nj, g_hi, m);
+    else fg_kernel<false><<<g, b, 0, c->stream>>>(c->u, c->v, c->F, c->G, c->g.pitch, c->g.ni, c->g.nj, g_hi, m);
     return cudaGetLastError();
 }
 
@@ -209,11 +215,27 @@ cudaError_t nsb_launch_fg_rhs(nsb_ctx* c, double dt, double gamma) {
 //   v = G - dt * ((pN - p)/dy)   j <= j_max-1        main.c:134 with dp_dy integration.c:108-110
 // and, over the interior after the update: signed max u, signed max v (seeded with m[0][0] like
 // io.c:124), sum p^2.
+struct UvRedArgs {
+    double* partials;        // [3][blocks]
+    double* bandvals;        // [3][n_chunks]
+    StepRed* red;
+    SlabRed sr;
+    unsigned long long round;
+    int chunk_rows, n_chunks, v_hi, seed00, world;
+};
+
+// One thread: the step reductions are complete.
+__device__ __forceinline__ void uv_red_store(StepRed* red, const double* out) {
+    red->u_max = out[0];
+    red->v_max = out[1];
+    red->sum_p2 = out[2];
+}
+
 template <bool RECIPD, bool UPDATE>
 __global__ void __launch_bounds__(256) update_uv_kernel(double* __restrict__ u, double* __restrict__ v,
                                                          const double* __restrict__ F, const double* __restrict__ G,
                                                          const double* __restrict__ p, long long pitch, int ni,
-                                                         int nj, MomCoef m, double* partials, StepRed* red) {
+                                                         int nj, MomCoef m, UvRedArgs ra) {
     __shared__ double sh[32];
     __shared__ int is_last;
     const int j = blockIdx.y + 1;
@@ -229,7 +251,7 @@ __global__ void __launch_bounds__(256) update_uv_kernel(double* __restrict__ u, 
                 un = __dsub_rn(F[o], __dmul_rn(m.dt, nsb_div<RECIPD>(__dsub_rn(p[o + 1], pc), m.dx, m.rdx)));
                 u[o] = un;
             }
-            if (j <= nj - 1) {
+            if (j <= ra.v_hi) {                                  // global j <= j_max-1 (main.c:134)
                 vn = __dsub_rn(G[o], __dmul_rn(m.dt, nsb_div<RECIPD>(__dsub_rn(p[o + pitch], pc), m.dy, m.rdy)));
                 v[o] = vn;
             }
@@ -246,41 +268,79 @@ __global__ void __launch_bounds__(256) update_uv_kernel(double* __restrict__ u, 
     double bv = block_max(mv, sh);
     double bs = block_sum(sp, sh);
     if (threadIdx.x == 0) {
-        partials[bid] = bu;
-        partials[nblk + bid] = bv;
-        partials[2 * nblk + bid] = bs;
+        ra.partials[bid] = bu;
+        ra.partials[nblk + bid] = bv;
+        ra.partials[2 * nblk + bid] = bs;
         __threadfence();
-        unsigned int t = atomicAdd(&red->ticket, 1u);
+        unsigned int t = atomicAdd(&ra.red->ticket, 1u);
         is_last = (t == (unsigned)nblk - 1);
     }
     __syncthreads();
     if (is_last) {
+        // band values: one band = the rows of one SOR chunk (never split between slabs), its block
+        // partials combined in a fixed order; the bands are then combined over ALL slabs in an order
+        // that depends on the global band count only (slab.cuh)
         __threadfence();
-        double a = -1.0e300, b = -1.0e300, s = 0.0;
-        for (int q = threadIdx.x; q < nblk; q += blockDim.x) {
-            a = fmax(a, __ldcg(partials + q));
-            b = fmax(b, __ldcg(partials + nblk + q));
-            s += __ldcg(partials + 2 * nblk + q);
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, gx = gridDim.x;
+        for (int b = warp; b < ra.n_chunks; b += 8) {
+            const int r0 = b * ra.chunk_rows;
+            const int rows = min(ra.chunk_rows, nj - r0);
+            const double a = warp_ordered_max(ra.partials + (size_t)r0 * gx, rows * gx, lane);
+            const double c = warp_ordered_max(ra.partials + nblk + (size_t)r0 * gx, rows * gx, lane);
+            const double s = warp_ordered_sum(ra.partials + 2 * (size_t)nblk + (size_t)r0 * gx, rows * gx, lane);
+            if (lane == 0) {
+                double aa = a, cc = c;
+                if (b == 0 && ra.seed00) {                       // io.c:124: the scan starts from m[0][0]
+                    const double u00 = u[(long long)NSB_ROW0 * pitch + NSB_COL0];
+                    const double v00 = v[(long long)NSB_ROW0 * pitch + NSB_COL0];
+                    aa = (u00 < a) ? a : u00;
+                    cc = (v00 < c) ? c : v00;
+                }
+                ra.bandvals[b] = aa;
+                ra.bandvals[ra.n_chunks + b] = cc;
+                ra.bandvals[2 * ra.n_chunks + b] = s;
+            }
         }
-        a = block_max(a, sh);
-        b = block_max(b, sh);
-        s = block_sum(s, sh);
-        if (threadIdx.x == 0) {
-            // io.c:124: the scan starts from m[0][0]
-            const double u00 = u[(long long)NSB_ROW0 * pitch + NSB_COL0];
-            const double v00 = v[(long long)NSB_ROW0 * pitch + NSB_COL0];
-            red->u_max = (u00 < a) ? a : u00;
-            red->v_max = (v00 < b) ? b : v00;
-            red->sum_p2 = s;
-            red->ticket = 0;
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) ra.red->ticket = 0;
+        slab_red_contribute(ra.sr, ra.round, 3, ra.bandvals);
+        if (ra.world == 1) {
+            slab_red_finish(ra.sr, ra.round, 3, 0x3u, sh);
+            if (threadIdx.x == 0) uv_red_store(ra.red, sh);
         }
     }
+}
+
+__global__ void __launch_bounds__(128) red_close_kernel(SlabRed sr, unsigned long long round, StepRed* red) {
+    __shared__ double out[4];
+    slab_red_finish(sr, round, 3, 0x3u, out);
+    if (threadIdx.x == 0) uv_red_store(red, out);
+}
+
+cudaError_t nsb_launch_red_close(nsb_ctx* c) {
+    red_close_kernel<<<1, 128, 0, c->stream>>>(nsb_slab_red(c), c->red_round, c->d_red);
+    return cudaGetLastError();
 }
 
 static void uv_grid(const nsb_ctx* c, dim3& g) {
     g = dim3(min((c->g.ni + 255) / 256, 4), c->g.nj);
 }
 
+static UvRedArgs uv_red_args(nsb_ctx* c) {
+    UvRedArgs ra;
+    memset(&ra, 0, sizeof ra);
+    ra.partials = c->d_red_partials; ra.bandvals = c->d_bandvals; ra.red = c->d_red;
+    ra.sr = nsb_slab_red(c);
+    ra.round = c->red_round;
+    ra.chunk_rows = c->chunk_rows; ra.n_chunks = c->n_chunks;
+    ra.v_hi = c->wall_top ? c->g.nj - 1 : c->g.nj;
+    ra.seed00 = c->wall_bottom ? 1 : 0;
+    ra.world = c->world;
+    return ra;
+}
+
+// Both launchers use reduction round c->red_round; the caller advances it (nsb_ph_*_finish).
 cudaError_t nsb_launch_update_uv(nsb_ctx* c, double dt) {
     MomCoef m = make_mom(c, dt, 0.0);
     dim3 g;
@@ -288,8 +348,9 @@ cudaError_t nsb_launch_update_uv(nsb_ctx* c, double dt) {
     const bool rd = (c->O.div_mode == NSB_DIV_RECIP) ||
                     (c->O.div_mode == NSB_DIV_AUTO && pow2(c->dx) && pow2(c->dy));
     double* p = c->pbuf[c->pcur];
-    if (rd) update_uv_kernel<true, true><<<g, 256, 0, c->stream>>>(c->u, c->v, c->F, c->G, p, c->g.pitch, c->g.ni, c->g.nj, m, c->d_red_partials, c->d_red);
-    else update_uv_kernel<false, true><<<g, 256, 0, c->stream>>>(c->u, c->v, c->F, c->G, p, c->g.pitch, c->g.ni, c->g.nj, m, c->d_red_partials, c->d_red);
+    UvRedArgs ra = uv_red_args(c);
+    if (rd) update_uv_kernel<true, true><<<g, 256, 0, c->stream>>>(c->u, c->v, c->F, c->G, p, c->g.pitch, c->g.ni, c->g.nj, m, ra);
+    else update_uv_kernel<false, true><<<g, 256, 0, c->stream>>>(c->u, c->v, c->F, c->G, p, c->g.pitch, c->g.ni, c->g.nj, m, ra);
     return cudaGetLastError();
 }
 
@@ -298,6 +359,6 @@ cudaError_t nsb_launch_reduce_uvp(nsb_ctx* c) {
     dim3 g;
     uv_grid(c, g);
     update_uv_kernel<true, false><<<g, 256, 0, c->stream>>>(c->u, c->v, c->F, c->G, c->pbuf[c->pcur], c->g.pitch,
-                                                            c->g.ni, c->g.nj, m, c->d_red_partials, c->d_red);
+                                                            c->g.ni, c->g.nj, m, uv_red_args(c));
     return cudaGetLastError();
 }

@@ -75,6 +75,50 @@ struct StepRed {
     int pad;
 };
 
+// ------------------------------------------------------------------ y-slab decomposition
+// Rank r of `world` owns the global rows j_lo+1 .. j_lo+nj (whole SOR chunks, so every reduction
+// band lies inside one rank).  Local row l is global row j_lo + l.  Local rows 0, -1, -2 and
+// nj+1 .. nj+3 hold the neighbour's rows (halo) where the slab ends inside the domain, and the
+// ghost / pad rows where it ends at a wall.  Everything a peer writes lives in one arena per rank
+// (one IPC handle); peers address it through the offsets of NsbSlabDesc.
+#define NSB_MAX_RANKS 16
+#define NSB_RED_Q 3                  // quantities per reduction round (u max, v max, sum) / (sum r^2)
+
+struct SlabSync {                    // in the arena; written by peers with system-scope stores
+    unsigned long long halo_epoch[2];              // [0] by the lower neighbour, [1] by the upper
+    unsigned long long red_arrived[NSB_MAX_RANKS]; // reduction rounds rank r has contributed to
+    int error;                                     // a wait timed out (set locally)
+    int pad;
+};
+
+struct NsbSlabDesc {                 // what a rank tells its peers (POD, travels through IPC / gloo / NCCL)
+    unsigned char ipc[64];           // cudaIpcMemHandle_t of the arena
+    unsigned long long base;         // arena device pointer in the owner's address space
+    long long pid;                   // owner process
+    int device, rank, world, nj, j_lo, n_strips, nbands_global, band0;
+    long long pitch;
+    long long off_u, off_v, off_G, off_rhs, off_p[2], off_sync, off_sorflag, off_gband;   // byte offsets in the arena
+    long long arena_bytes;
+    unsigned long long reserved[4];
+};
+
+struct SlabPeer {                    // a peer as seen from this rank (device pointers valid HERE)
+    unsigned char* base;             // mapped arena
+    double *u, *v, *G, *rhs, *p[2];
+    SlabSync* sync;
+    unsigned long long* sorflag;     // [2][n_strips]: [0] written by ITS lower neighbour, [1] by its upper
+    double* gband;                   // [2 parities][NSB_RED_Q][nbands_global]
+    int nj;
+    bool mapped_ipc;
+};
+
+// By-value kernel argument for the collective reductions.
+struct SlabRed {
+    int rank, world, band0, nb_local, nb_global;
+    SlabSync* sync[NSB_MAX_RANKS];
+    double* gband[NSB_MAX_RANKS];
+};
+
 struct nsb_ctx {
     nsb_params P;
     nsb_options O;
@@ -91,6 +135,21 @@ struct nsb_ctx {
     double* pbuf[2];
     int pcur;              // pbuf[pcur] holds the current pressure
     double* scratch;       // one grid of staging space (layout conversion)
+    // slab decomposition (world == 1: the whole domain)
+    int rank, world;
+    int J;                 // global j_max (P.j_max); g.nj is the LOCAL row count
+    int j_lo;              // global row of local row l is j_lo + l
+    bool wall_bottom, wall_top;
+    int band0, nbands_global;
+    unsigned char* arena; size_t arena_bytes;
+    NsbSlabDesc desc;
+    SlabPeer peer[NSB_MAX_RANKS];      // peer[rank] is this rank itself
+    bool connected;
+    SlabSync* d_sync; unsigned long long* d_sorflag; double* d_gband;
+    unsigned long long seq;            // SOR iterations executed so far (halo flag values)
+    unsigned long long red_round;      // collective reduction rounds completed so far
+    unsigned long long epoch[2];       // halo exchanges pushed to [0] the lower, [1] the upper neighbour
+    unsigned long long epoch_in[2];    // halo exchanges expected from [0] the lower, [1] the upper neighbour
     // SOR machinery
     SorCtl* d_ctl; SorCtl* h_ctl;       // device / pinned host
     double* d_partials; int n_partials;
@@ -98,6 +157,7 @@ struct nsb_ctx {
     // step reductions
     StepRed* d_red; StepRed* h_red;
     double* d_red_partials; int n_red_partials;
+    double* d_bandvals;    // [NSB_RED_Q][n_chunks] band values staged for the collective reduction
     bool red_valid;        // h_red holds max u, max v, sum p^2 of the current fields
     double* h_stage; size_t h_stage_elems;   // pinned staging for uploads/downloads
     cudaEvent_t ev0, ev1, ev_chk[2];
@@ -128,3 +188,27 @@ int nsb_sor_resident_supported(const nsb_ctx* c);
 cudaError_t nsb_launch_sor_resident(nsb_ctx* c, int max_it, int check);
 
 void nsb_sor_plan(nsb_ctx* c);
+
+// ---- slab decomposition (slab.cu / step.cu)
+SlabRed nsb_slab_red(const nsb_ctx* c);
+cudaError_t nsb_launch_sor_close(nsb_ctx* c, int it, int check);            // world > 1: wait + combine + test
+cudaError_t nsb_launch_red_close(nsb_ctx* c);                               // world > 1: finish the step reduction
+// exchange kinds
+enum { NSB_X_UV = 0, NSB_X_G = 1, NSB_X_P = 2, NSB_X_RHS = 3 };
+cudaError_t nsb_launch_halo_push(nsb_ctx* c, int kind);
+cudaError_t nsb_launch_halo_wait(nsb_ctx* c, int kind);
+int nsb_create_slab_internal(const nsb_params* P, const nsb_options* opt, int rank, int world, nsb_ctx** out);
+int nsb_fail(nsb_ctx* c, int code, const char* fmt, ...);
+int nsb_get_value(nsb_ctx* c, int i, int l, double* u_c, double* v_c);
+int nsb_xfer_rows(nsb_ctx* c, int field, double* host, int l0, int nrows, int up);
+extern "C" int nsb_slab_error(nsb_ctx* c);
+extern "C" int nsb_slab_export(const nsb_ctx* c, void* desc_out);
+extern "C" int nsb_slab_connect(nsb_ctx* c, const void* descs);
+// phases of one time step; every one is collective over the ranks of a decomposition
+int nsb_ph_reduce_launch(nsb_ctx* c);     // max u, max v, sum p^2 when the cache is stale
+int nsb_ph_reduce_finish(nsb_ctx* c);
+int nsb_ph_bc(nsb_ctx* c, double t);
+int nsb_ph_sor_begin(nsb_ctx* c);
+int nsb_ph_sor_end(nsb_ctx* c, int iters);
+int nsb_ph_update_launch(nsb_ctx* c, double dt);
+int nsb_ph_update_finish(nsb_ctx* c);

@@ -25,7 +25,7 @@ __global__ void sor_begin_kernel(SorCtl* ctl, const StepRed* red, double eps, lo
 
 cudaError_t nsb_launch_sor_begin(nsb_ctx* c) {
     sor_begin_kernel<<<1, 32, 0, c->stream>>>(c->d_ctl, c->d_red, c->P.epsilon,
-                                              (long long)c->g.ni * (long long)c->g.nj);
+                                              (long long)c->g.ni * (long long)c->J);      // global cell count
     return cudaGetLastError();
 }
 
@@ -141,7 +141,7 @@ cudaError_t nsb_launch_sor_simple_iter(nsb_ctx* c, int it, double* p, int check)
 // wall-adjacent red cell, the pre-black value of a wall-adjacent black cell.  The pre-black value
 // of the last iteration is what the other ping-pong buffer still holds.
 __global__ void sor_finish_ghosts_kernel(double* pf, const double* __restrict__ pv, long long pitch,
-                                         int ni, int nj) {
+                                         int ni, int nj, int wall_bottom, int wall_top) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     double* f = pf + (long long)NSB_ROW0 * pitch + NSB_COL0;
     const double* v = pv + (long long)NSB_ROW0 * pitch + NSB_COL0;
@@ -153,14 +153,15 @@ __global__ void sor_finish_ghosts_kernel(double* pf, const double* __restrict__ 
     }
     if (t < ni) {
         int i = t + 1;
-        f[i] = ((i + 1) & 1) ? v[pitch + i] : f[pitch + i];
+        if (wall_bottom) f[i] = ((i + 1) & 1) ? v[pitch + i] : f[pitch + i];
         long long r = (long long)nj * pitch;
-        f[r + pitch + i] = ((i + nj) & 1) ? v[r + i] : f[r + i];
+        if (wall_top) f[r + pitch + i] = ((i + nj) & 1) ? v[r + i] : f[r + i];   // slab boundary: the neighbour's row stays
     }
 }
 
 cudaError_t nsb_launch_sor_finish_ghosts(nsb_ctx* c, double* pfinal, const double* pprev) {
     const int n = max(c->g.ni, c->g.nj);
-    sor_finish_ghosts_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(pfinal, pprev, c->g.pitch, c->g.ni, c->g.nj);
+    sor_finish_ghosts_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(pfinal, pprev, c->g.pitch, c->g.ni, c->g.nj,
+                                                                     c->wall_bottom ? 1 : 0, c->wall_top ? 1 : 0);
     return cudaGetLastError();
 }

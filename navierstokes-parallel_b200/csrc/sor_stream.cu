@@ -30,8 +30,11 @@
 //   - residual: per-warp partial (fixed order), last block of the grid adds the partials in a fixed
 //     order, takes sqrt(sum/(i_max*j_max)) (main.cu:588), compares with eps*(norm_p+1.5)
 //     (main.cu:713) and raises the device-side converged flag; later launches exit at once.
+#include <string.h>
+
 #include "nsb_internal.h"
 #include "nsb_math.cuh"
+#include "slab.cuh"
 
 #ifndef SOR_WARPS
 #define SOR_WARPS 4
@@ -56,13 +59,23 @@ struct SorStreamArgs {
     const double* __restrict__ rhs;
     long long pitch;
     int ni, nj;
-    int chunk_rows, n_strips, n_tasks;
+    int chunk_rows, n_strips, n_tasks, n_chunks;
     int n_groups;            // pitch / 4
     int it, check;
     unsigned int zero;       // always 0; opaque to the compiler
     SorCoef k;
     double* partials;
+    double* bandvals;
     SorCtl* ctl;
+    // y-slab decomposition (world == 1: unused)
+    int world, wall_bottom, wall_top, down_nj;
+    unsigned long long seq;                  // SOR iterations executed before this one, all solves
+    unsigned long long round;                // reduction round of this iteration
+    double* down_pout; double* up_pout;      // the neighbours' output buffers (storage row 0)
+    const unsigned long long* flag_from_down; const unsigned long long* flag_from_up;   // in my arena
+    unsigned long long* down_flag; unsigned long long* up_flag;                         // in theirs
+    int* err;
+    SlabRed red;
 };
 
 // ---------------------------------------------------------------- mbarrier / bulk-copy PTX
@@ -104,22 +117,15 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 
-// All threads of the LAST block of an iteration: fixed-order sum of the partials, convergence test.
-__device__ __forceinline__ void sor_close_iteration(const double* partials, int n, SorCtl* ctl, int it,
-                                                    long long cells, double* sh) {
-    double s = 0.0;
-    for (int q = threadIdx.x; q < n; q += blockDim.x) s += __ldcg(partials + q);
-    double total = block_sum(s, sh);
-    if (threadIdx.x == 0) {
-        double res = sqrt(total / (double)cells);          // main.cu:588
-        ctl->sum_r2 = total;
-        ctl->res = res;
-        ctl->iters = it + 1;
-        if (res <= ctl->thresh) ctl->converged = 1;         // main.cu:713
-        ctl->ticket = 0;
-        __threadfence();
-        sor_publish(ctl);
-    }
+// One thread: closes iteration `it` with the global sum of r^2.
+__device__ __forceinline__ void sor_close_iteration(double total, SorCtl* ctl, int it, long long cells) {
+    double res = sqrt(total / (double)cells);              // main.cu:588
+    ctl->sum_r2 = total;
+    ctl->res = res;
+    ctl->iters = it + 1;
+    if (res <= ctl->thresh) ctl->converged = 1;             // main.cu:713
+    __threadfence();
+    sor_publish(ctl);
 }
 
 // Per-lane geometry, fixed for the whole task.
@@ -152,6 +158,11 @@ __device__ __forceinline__ void refresh_ghost_columns(double (&X)[4], const Lane
 struct TaskCtx {
     int jstart, jc0, jc1;
     int nj;
+    int rlo, rhi;             // rows that take updates: 1..nj at walls, -1 / nj+2 at a slab boundary
+    bool wall_bottom, wall_top;
+    bool push_down, push_up;  // this task owns rows of the neighbour's halo
+    double* down_col; double* up_col;   // neighbour's pout, this lane's column group, row 0 of its storage
+    int down_nj;
     long long pitch;
     double* pout_row;         // &pout[row of the black update of the current step][this lane's group]
     const double* lds_lane;   // generic pointer: this warp's ring + 4 * lane doubles
@@ -254,15 +265,15 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
     // ---- colour 0 (red) on row D = j-1; neighbours C (j-2, black cells still old) and E (j)
     {
         const int r = j - 1;
-        const bool row_in = !EY || ((r >= 1) && (r <= t.nj));
+        const bool row_in = !EY || ((r >= t.rlo) && (r <= t.rhi));
         double (&X)[4] = P[sD];
         if (EX) refresh_ghost_columns(X, lg);                           // main.cu:686
         if (EY) {
-            if (r == 1) {
+            if (r == 1 && t.wall_bottom) {
 #pragma unroll
                 for (int k = 0; k < 4; k++) P[sC][k] = X[k];            // p[i][0] = p[i][1]
             }
-            if (r == t.nj) {
+            if (r == t.nj && t.wall_top) {
 #pragma unroll
                 for (int k = 0; k < 4; k++) P[sE][k] = X[k];            // p[i][j_max+1] = p[i][j_max]
             }
@@ -283,15 +294,15 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
     // ---- colour 1 (black) on row C = j-2; neighbours B (j-3, final) and D (j-1, red done)
     {
         const int r = j - 2;
-        const bool row_in = !EY || ((r >= 1) && (r <= t.nj));
+        const bool row_in = !EY || ((r >= t.rlo) && (r <= t.rhi));
         double (&X)[4] = P[sC];
         if (EX) refresh_ghost_columns(X, lg);                           // main.cu:694
         if (EY) {
-            if (r == 1) {
+            if (r == 1 && t.wall_bottom) {
 #pragma unroll
                 for (int k = 0; k < 4; k++) P[sB][k] = X[k];
             }
-            if (r == t.nj) {
+            if (r == t.nj && t.wall_top) {
 #pragma unroll
                 for (int k = 0; k < 4; k++) P[sD][k] = X[k];
             }
@@ -312,6 +323,20 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
             double2* q = reinterpret_cast<double2*>(t.pout_row);
             q[0] = make_double2(X[0], X[1]);
             q[1] = make_double2(X[2], X[3]);
+            if (EY) {
+                // y-slab halo: the three rows next to a slab boundary also go straight into the
+                // neighbour's halo rows over NVLink (peer store), SURVEY 8e
+                if (t.push_down && r <= 3) {
+                    double2* h = reinterpret_cast<double2*>(t.down_col + (long long)(t.down_nj + r + NSB_ROW0) * t.pitch);
+                    h[0] = make_double2(X[0], X[1]);
+                    h[1] = make_double2(X[2], X[3]);
+                }
+                if (t.push_up && r >= t.nj - 2) {
+                    double2* h = reinterpret_cast<double2*>(t.up_col + (long long)(r - t.nj + NSB_ROW0) * t.pitch);
+                    h[0] = make_double2(X[0], X[1]);
+                    h[1] = make_double2(X[2], X[3]);
+                }
+            }
         }
         t.pout_row += t.pitch;
     }
@@ -365,7 +390,8 @@ __device__ __forceinline__ double sor_run_task(TaskCtx& t, const SorCoef& kf, co
 #ifdef SOR_NO_LEAN
         const bool clean = false;
 #else
-        const bool clean = (jb - 3 >= t.jc0) && (jb + 5 <= t.jc1) && (jb + 7 <= t.nj);
+        const bool clean = (jb - 3 >= t.jc0) && (jb + 5 <= t.jc1) && (jb + 7 <= t.nj) &&
+                           !(t.push_down && jb - 2 <= 3) && !(t.push_up && jb + 5 >= t.nj - 2);
 #endif
         if (EX) sor_block8<RECIP, true, true>(P, R, sb, t, kf, lg, acc);
         else if (clean) sor_block8<RECIP, false, false>(P, R, sb, t, kf, lg, acc);
@@ -389,7 +415,12 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int task = blockIdx.x * SOR_WARPS + warp;
     if (task < a.n_tasks) {
-        const int strip = task % a.n_strips, chunk = task / a.n_strips;
+        const int strip = task % a.n_strips;
+        int chunk = task / a.n_strips;
+        if (a.world > 1 && a.n_chunks > 1) {
+            // slab boundaries first: their rows reach the neighbours a whole launch before they are read
+            chunk = (chunk == 0) ? 0 : (chunk == 1) ? a.n_chunks - 1 : chunk - 1;
+        }
         const int g0 = strip * NSB_STRIP_GROUPS;             // first column group of the strip
         const int g = g0 + lane;                             // column group of this lane
         const int i0 = g * NSB_GROUP - NSB_COL0;             // i of column k = 0
@@ -417,6 +448,11 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
         t.jc1 = min(t.jc0 + a.chunk_rows - 1, a.nj);
         t.jstart = t.jc0 - 3;                                // even, because chunk_rows is even
         t.nj = a.nj;
+        t.wall_bottom = a.wall_bottom != 0; t.wall_top = a.wall_top != 0;
+        t.rlo = t.wall_bottom ? 1 : -1;
+        t.rhi = t.wall_top ? a.nj : a.nj + 2;
+        t.push_down = !t.wall_bottom && t.jc0 <= 3;
+        t.push_up = !t.wall_top && t.jc1 >= a.nj - 2;
         t.pitch = a.pitch;
         t.lane = lane;
         t.zero = a.zero;
@@ -427,12 +463,30 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
         t.j_next = t.jstart;
         t.j_limit = min(t.jc1 + 3, a.nj + 3);
         t.pout_row = a.pout + row_first - 2 * a.pitch + coff + (long long)lane * NSB_GROUP;
+        t.down_col = a.down_pout + coff + (long long)lane * NSB_GROUP;
+        t.up_col = a.up_pout + coff + (long long)lane * NSB_GROUP;
+        t.down_nj = a.down_nj;
         const int groups_here = min(32, a.n_groups - g0);
         t.copy_bytes = (uint32_t)groups_here * 32u;
         unsigned char* ring = smem_raw + warp * SOR_WARP_SMEM;
         t.lds_lane = reinterpret_cast<const double*>(ring) + lane * NSB_GROUP;
         t.smem_base = smem_u32(ring);
         t.bar_base = smem_u32(smem_raw + SOR_WARPS * SOR_WARP_SMEM + warp * 2 * SOR_NST * 8);
+
+        // ---- y-slab: the halo rows this task reads were stored by the neighbour's launch seq-1
+        if (a.world > 1) {
+            const bool need_down = !t.wall_bottom && t.jc0 - 3 <= 0;
+            const bool need_up = !t.wall_top && t.jc1 + 3 >= a.nj + 1;
+            if (lane < 3) {
+                const int sidx = strip - 1 + lane;           // the columns read belong to strips s-1, s, s+1
+                if (sidx >= 0 && sidx < a.n_strips) {
+                    if (need_down) spin_until_ge(a.flag_from_down + sidx, a.seq, a.err);
+                    if (need_up) spin_until_ge(a.flag_from_up + sidx, a.seq, a.err);
+                }
+            }
+            __syncwarp();
+            asm volatile("fence.proxy.async;" ::: "memory");   // peer stores (generic) -> TMA reads (async)
+        }
 
         if (lane == 0) {
 #pragma unroll
@@ -451,10 +505,20 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
         if (edge_strip) acc = sor_run_task<RECIP, true>(t, a.k, lg);
         else acc = sor_run_task<RECIP, false>(t, a.k, lg);
         acc = warp_sum(acc);
-        if (lane == 0) a.partials[task] = acc;
+        if (lane == 0) a.partials[chunk * a.n_strips + strip] = acc;
+
+        if (t.push_down || t.push_up) {                      // halo rows are out: tell the neighbour(s)
+            __threadfence_system();
+            __syncwarp();
+            if (lane == 0) {
+                if (t.push_down) st_release_sys(a.down_flag + strip, a.seq + 1ull);
+                if (t.push_up) st_release_sys(a.up_flag + strip, a.seq + 1ull);
+            }
+        }
     }
 
-    // ---- last block closes the iteration
+    // ---- last block: band sums (one band = one chunk of rows, strips added in a fixed order),
+    //      contributed to the collective reduction; with one slab it also closes the iteration
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -464,8 +528,35 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
     __syncthreads();
     if (is_last) {
         __threadfence();
-        sor_close_iteration(a.partials, a.n_tasks, a.ctl, a.it, a.k.cells, sh);
+        for (int b = warp; b < a.n_chunks; b += SOR_WARPS) {
+            const double v = warp_ordered_sum(a.partials + (size_t)b * a.n_strips, a.n_strips, lane);
+            if (lane == 0) a.bandvals[b] = v;
+        }
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) a.ctl->ticket = 0;
+        slab_red_contribute(a.red, a.round, 1, a.bandvals);
+        if (a.world == 1) {
+            slab_red_finish(a.red, a.round, 1, 0u, sh);
+            if (threadIdx.x == 0) sor_close_iteration(sh[0], a.ctl, a.it, a.k.cells);
+        }
     }
+}
+
+// world > 1: the closing of an iteration is its own one-block kernel, so that the sweep kernel never
+// waits for another GPU (and so that the ranks can be emulated in lock step on one device).
+__global__ void __launch_bounds__(128) sor_close_kernel(SlabRed red, unsigned long long round, SorCtl* ctl, int it,
+                                                        long long cells, int check) {
+    __shared__ double out[4];
+    if (check && *((volatile int*)&ctl->converged)) return;
+    slab_red_finish(red, round, 1, 0u, out);
+    if (threadIdx.x == 0) sor_close_iteration(out[0], ctl, it, cells);
+}
+
+cudaError_t nsb_launch_sor_close(nsb_ctx* c, int it, int check) {
+    sor_close_kernel<<<1, 128, 0, c->stream>>>(nsb_slab_red(c), c->red_round + (unsigned long long)it, c->d_ctl, it,
+                                               (long long)c->g.ni * (long long)c->J, check);
+    return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------------------
@@ -512,11 +603,22 @@ void nsb_sor_plan(nsb_ctx* c) {
     c->n_partials = c->n_chunks * c->n_strips;
 }
 
+SlabRed nsb_slab_red(const nsb_ctx* c) {
+    SlabRed r;
+    memset(&r, 0, sizeof r);
+    r.rank = c->rank; r.world = c->world; r.band0 = c->band0; r.nb_local = c->n_chunks; r.nb_global = c->nbands_global;
+    for (int k = 0; k < c->world; k++) { r.sync[k] = c->peer[k].sync; r.gband[k] = c->peer[k].gband; }
+    return r;
+}
+
+// `it` = iteration number inside the current solve.  pin / pout are pbuf[x] / pbuf[x ^ 1] of this
+// rank; the neighbours' output buffer of the same parity receives the halo rows.
 cudaError_t nsb_launch_sor_stream_iter(nsb_ctx* c, int it, const double* pin, double* pout, int check) {
     SorStreamArgs a;
+    memset(&a, 0, sizeof a);
     a.pin = pin; a.pout = pout; a.rhs = c->rhs;
     a.pitch = c->g.pitch; a.ni = c->g.ni; a.nj = c->g.nj;
-    a.chunk_rows = c->chunk_rows; a.n_strips = c->n_strips; a.n_tasks = c->n_partials;
+    a.chunk_rows = c->chunk_rows; a.n_strips = c->n_strips; a.n_tasks = c->n_partials; a.n_chunks = c->n_chunks;
     a.n_groups = (int)(c->g.pitch / NSB_GROUP);
     a.it = it; a.check = check; a.zero = 0u;
     const double dx2 = c->dx * c->dx, dy2 = c->dy * c->dy;
@@ -524,8 +626,30 @@ cudaError_t nsb_launch_sor_stream_iter(nsb_ctx* c, int it, const double* pin, do
     a.k.w = c->P.omega / (2.0 * (1.0 / dx2 + 1.0 / dy2));
     a.k.dx2 = dx2; a.k.dy2 = dy2; a.k.rdx2 = 1.0 / dx2; a.k.rdy2 = 1.0 / dy2;
     a.k.inv_cells_unused = 0.0;
-    a.k.cells = (long long)c->g.ni * (long long)c->g.nj;
-    a.partials = c->d_partials; a.ctl = c->d_ctl;
+    a.k.cells = (long long)c->g.ni * (long long)c->J;          // main.cu:588: the GLOBAL cell count
+    a.partials = c->d_partials; a.bandvals = c->d_bandvals; a.ctl = c->d_ctl;
+    a.world = c->world; a.wall_bottom = c->wall_bottom; a.wall_top = c->wall_top;
+    a.seq = c->seq + (unsigned long long)it;
+    a.round = c->red_round + (unsigned long long)it;
+    a.red = nsb_slab_red(c);
+    a.err = &c->d_sync->error;
+    const int par = (pout == c->pbuf[1]) ? 1 : 0;
+    a.down_pout = pout; a.up_pout = pout; a.down_nj = 0;
+    a.flag_from_down = c->d_sorflag; a.flag_from_up = c->d_sorflag + c->n_strips;
+    a.down_flag = c->d_sorflag; a.up_flag = c->d_sorflag;
+    if (c->world > 1) {
+        if (!c->connected) return cudaErrorNotReady;
+        if (!c->wall_bottom) {
+            const SlabPeer& d = c->peer[c->rank - 1];
+            a.down_pout = d.p[par]; a.down_nj = d.nj;
+            a.down_flag = d.sorflag + c->n_strips;             // I am its UPPER neighbour
+        }
+        if (!c->wall_top) {
+            const SlabPeer& u = c->peer[c->rank + 1];
+            a.up_pout = u.p[par];
+            a.up_flag = u.sorflag;                             // I am its LOWER neighbour
+        }
+    }
     const int blocks = (a.n_tasks + SOR_WARPS - 1) / SOR_WARPS;
     if (c->use_recip) sor_stream_kernel<true><<<blocks, SOR_THREADS, SOR_SMEM_BYTES, c->stream>>>(a);
     else sor_stream_kernel<false><<<blocks, SOR_THREADS, SOR_SMEM_BYTES, c->stream>>>(a);
