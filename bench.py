@@ -134,7 +134,9 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--size", type=int, default=8192)
+    ap.add_argument("--size", type=int, default=8192, help="i_max (and j_max per GPU with weak scaling)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="N > 1: weak = size x (size*N) cells, one size^2 slab per GPU; strong = size^2 cut into N slabs")
     ap.add_argument("--max-it", type=int, default=500)
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -147,21 +149,34 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     size, max_it = args.size, args.max_it
-    cells = float(size) * float(size)
-    workload = (f"synthetic lid-driven cavity {size}x{size} FP64, Re=1000, omega=1.7, eps=1e-4, "
-                f"max_it={max_it} (BASELINE.json configs[2])")
-    config = {"workload": workload, "grid": [size, size], "max_it": max_it, "parallelism": f"y-slabs x{world}" if world > 1 else "single GPU",
-              "l2": "inputs larger than L2 (537 MB per grid at 8192^2 vs 126 MB L2); no flush"}
+    ni = size
+    nj = size * world if (world > 1 and args.scaling == "weak") else size     # global rows
+    cells = float(ni) * float(nj)                                             # global cells
+    if world == 1:
+        workload = (f"synthetic lid-driven cavity {size}x{size} FP64, Re=1000, omega=1.7, eps=1e-4, "
+                    f"max_it={max_it} (BASELINE.json configs[2])")
+        par = "single GPU"
+    elif args.scaling == "weak":
+        workload = (f"synthetic lid-driven cavity {ni}x{nj} FP64 ({size}^2 cells per GPU, box {1}x{world}), Re=1000, "
+                    f"omega=1.7, eps=1e-4, max_it={max_it} (BASELINE.json configs[4], weak scaling of configs[2])")
+        par = f"y-slabs x{world}, halo rows pushed over NVLink inside the SOR kernel, one process per GPU"
+    else:
+        workload = (f"synthetic lid-driven cavity {ni}x{nj} FP64 cut into {world} y-slabs, Re=1000, omega=1.7, "
+                    f"eps=1e-4, max_it={max_it} (BASELINE.json configs[3], strong scaling)")
+        par = f"y-slabs x{world}, halo rows pushed over NVLink inside the SOR kernel, one process per GPU"
+    config = {"workload": workload, "grid": [ni, nj], "max_it": max_it, "parallelism": par,
+              "l2": f"inputs larger than L2 ({ni * (nj // world) * 8 / 1e6:.0f} MB per grid per GPU vs 126 MB L2); no flush"}
+    scaling = "weak" if (world == 1 or args.scaling == "weak") else "strong"
 
     if args.impl == "reference":
         if rank != 0:
             return 0
         # bounded sample: 1 lexicographic sweep over the 8192^2 grid ~ 1.1 s on one core
-        ips = 2 if size >= 4096 else max(2, int(2e8 / cells))
+        ips = 2 if size >= 4096 else max(2, int(2e8 / (float(size) * size)))
         b = cpu_reference_sor(size, ips, max(1, args.steps), max(1, min(args.warmup, 1)))
         line = {"impl": "reference", "metric": "sor_mlups", "value": b["value"], "unit": "MLUPS", "n_gpus": args.gpus,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": b["ms_per_step"], "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+                "scaling": scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
                 "cpu_baseline": {k: b[k] for k in ("value", "unit", "cores", "kind", "sample")},
                 "e2e": {"value": b["value"], "unit": "MLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
@@ -183,8 +198,30 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    P = workload_params(m, size, max_it)
-    s = m.Solver(P, device=local, sor_engine=args.engine, chunk_rows=args.chunk_rows)
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        tt = torch.tensor([x], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        tt = torch.tensor([x], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.SUM)
+        return float(tt.item())
+
+    P = m.make_params(problem=1, f=1.0, i_max=ni, j_max=nj, a=1.0, b=float(nj) / float(ni), T=1.0e9, Re=1000.0,
+                      g_x=0.0, g_y=0.0, tau=1.0, omega=1.7, epsilon=1e-4, max_it=max_it, n_print=1)
+    if world == 1:
+        s = m.Solver(P, device=local, sor_engine=args.engine, chunk_rows=args.chunk_rows)
+        nj_local = nj
+    else:
+        # one slab per process; NCCL only carries the 256-byte slab descriptors, once
+        s = m.SlabSolver(P, rank, world, m.torch_all_gather(), device=local, chunk_rows=args.chunk_rows)
+        nj_local = s.nj
+    cells_local = float(ni) * float(nj_local)
     stream = torch.cuda.ExternalStream(s.stream, device=torch.device("cuda", local))
 
     # ---- device-resident steps
@@ -197,6 +234,7 @@ def main():
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     w0 = time.time()
+    l0 = s.launch_count()
     e0.record(stream)
     iters = 0
     for _ in range(args.steps):
@@ -204,76 +242,93 @@ def main():
     e1.record(stream)
     barrier()
     w1 = time.time()
-    ms = e0.elapsed_time(e1)
+    launches = int(sum_over_ranks(float(s.launch_count() - l0)))
+    ms = max_over_ranks(e0.elapsed_time(e1))
     clocks = sampler.stop(w0, w1)
-    if world > 1:
-        tt = torch.tensor([ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        ms = float(tt.item())
-    total_lups = float(iters) * cells * world          # replicas / slabs: every rank did `iters` sweeps of its cells
+    total_lups = float(iters) * cells                      # every iteration updates every cell of the global grid once
     value = total_lups / (ms * 1e-3) / 1e6
-    launches = args.steps * (4 + 2 + 1 + (iters // max(1, args.steps)) + 1 + 1)
 
     # ---- dominant kernel alone: average launch duration over a fixed batch of iterations
     barrier()
     n_k = 100
     s.sor_iterations(10)
+    barrier()
     k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     k0.record(stream)
     s.sor_iterations(n_k)
     k1.record(stream)
     torch.cuda.synchronize()
-    k_ms = k0.elapsed_time(k1) / n_k
+    k_ms = max_over_ranks(k0.elapsed_time(k1) / n_k)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    achieved = 24.0 * cells / (k_ms * 1e-3) / 1e9
+    achieved = 24.0 * cells_local / (k_ms * 1e-3) / 1e9
     traffic = None
     try:
         traffic = json.load(open(os.path.join(ROOT, "profiles", "sor_stream_traffic.json"))).get("dram_bytes_per_launch")
     except Exception:
         pass
     roofline = {"bound": "hbm", "kernel": "sor_stream_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic,
+                "frac": achieved / peak, "traffic": traffic if (world == 1 and size == 8192) else None,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
-                "algorithmic_bytes_per_launch": 24.0 * cells, "launch_ms": k_ms,
-                "kernel_mlups": cells / (k_ms * 1e-3) / 1e6}
+                "algorithmic_bytes_per_launch": 24.0 * cells_local, "launch_ms": k_ms,
+                "kernel_mlups": cells_local / (k_ms * 1e-3) / 1e6,
+                "note": "per GPU: one launch = one red+black+residual iteration over this GPU's cells, 24 B per cell"}
 
-    # ---- end to end: host grids in, host grids out (nsb_timestep), pinned host memory
+    # ---- end to end: host grids in, host grids out, pinned host memory, copies inside the timed region
     e2e = None
     if not args.no_e2e:
         L = m.lib()
-        ni = nj = size
-        hu = torch.zeros((ni + 1, nj + 2), dtype=torch.float64).pin_memory()
-        hv = torch.zeros((ni + 2, nj + 1), dtype=torch.float64).pin_memory()
-        hp = torch.zeros((ni + 2, nj + 2), dtype=torch.float64).pin_memory()
-        ur, vr, pr = m.rows(hu.numpy()), m.rows(hv.numpy()), m.rows(hp.numpy())
-        null = C.cast(None, m.dbl_pp)
-        info = m.StepInfo()
         tt_, it2 = 0.0, 0
-        rc = L.nsb_timestep(C.byref(P), tt_, ur, vr, pr, null, null, null, C.byref(info))     # warm-up (allocates)
-        assert rc == 0, rc
-        tt_ += info.dt
+        if world == 1:
+            # the reference-shaped host-grid call: nsb_timestep(double** u, v, p)
+            hu = torch.zeros((ni + 1, nj + 2), dtype=torch.float64).pin_memory()
+            hv = torch.zeros((ni + 2, nj + 1), dtype=torch.float64).pin_memory()
+            hp = torch.zeros((ni + 2, nj + 2), dtype=torch.float64).pin_memory()
+            ur, vr, pr = m.rows(hu.numpy()), m.rows(hv.numpy()), m.rows(hp.numpy())
+            null = C.cast(None, m.dbl_pp)
+            info = m.StepInfo()
+
+            def one_step(tq):
+                rc = L.nsb_timestep(C.byref(P), tq, ur, vr, pr, null, null, null, C.byref(info))
+                assert rc == 0, rc
+                return info.dt, info.sor_iters
+            bi = (hu.numel() + hv.numel() + hp.numel()) * 8
+            api = "nsb_timestep(double** u, v, p) -- upload, whole step in HBM, download"
+        else:
+            # each rank keeps its slab (rows 0 .. nj_local+1) of u, v, p in pinned host memory
+            hb = [torch.zeros((nj_local + 2, ni + 2), dtype=torch.float64).pin_memory() for _ in range(3)]
+            ptrs = [C.cast(x.data_ptr(), m.dbl_p) for x in hb]
+            fields = (m.U, m.V, m.P)
+
+            def one_step(tq):
+                for f, q in zip(fields, ptrs):
+                    rc = L.nsb_upload(s._h, f, q, m.LAYOUT_XFAST)
+                    assert rc == 0, rc
+                inf = s.step(tq)
+                for f, q in zip(fields, ptrs):
+                    rc = L.nsb_download(s._h, f, q, m.LAYOUT_XFAST)
+                    assert rc == 0, rc
+                return inf["dt"], inf["sor_iters"]
+            bi = sum(x.numel() for x in hb) * 8 * world
+            api = "per rank: nsb_upload(u, v, p slab) -> nsb_step -> nsb_download(u, v, p slab)"
+        dt_, _ = one_step(tt_)                                   # warm-up (allocates)
+        tt_ += dt_
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.e2e_steps):
-            rc = L.nsb_timestep(C.byref(P), tt_, ur, vr, pr, null, null, null, C.byref(info))
-            assert rc == 0, rc
-            tt_ += info.dt; it2 += info.sor_iters
+            dt_, k_ = one_step(tt_)
+            tt_ += dt_; it2 += k_
         barrier()
-        el = time.perf_counter() - t0
-        if world > 1:
-            t2 = torch.tensor([el], device="cuda", dtype=torch.float64)
-            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
-            el = float(t2.item())
-        bi = (hu.numel() + hv.numel() + hp.numel()) * 8
-        e2e = {"value": float(it2) * cells * world / el / 1e6, "unit": "MLUPS", "h2d_bytes_per_step": bi,
-               "d2h_bytes_per_step": bi, "steps": args.e2e_steps, "ms_per_step": el / args.e2e_steps * 1e3,
-               "api": "nsb_timestep(double** u, v, p) -- upload, whole step in HBM, download"}
-        L.nsb_host_api_reset()
+        el = max_over_ranks(time.perf_counter() - t0)
+        e2e = {"value": float(it2) * cells / el / 1e6, "unit": "MLUPS", "h2d_bytes_per_step": bi,
+               "d2h_bytes_per_step": bi, "steps": args.e2e_steps, "ms_per_step": el / args.e2e_steps * 1e3, "api": api}
+        if world == 1:
+            L.nsb_host_api_reset()
+    barrier()
     s.close()
 
     cpu = None
@@ -283,10 +338,10 @@ def main():
 
     if rank == 0:
         line = {"metric": "sor_mlups", "value": value, "unit": "MLUPS", "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": scaling,
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
                 "timesteps_per_s": args.steps / (ms * 1e-3), "sor_iters_per_step": iters / max(1, args.steps),
-                "hbm_gbs_whole_step": (80.0 + 24.0 * iters / max(1, args.steps)) * cells * world * args.steps / (ms * 1e-3) / 1e9,
+                "hbm_gbs_whole_step": (80.0 + 24.0 * iters / max(1, args.steps)) * cells * args.steps / (ms * 1e-3) / 1e9,
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
         print(json.dumps(line))
     if world > 1:

@@ -142,6 +142,8 @@ int nsb_run(nsb_ctx* ctx, int max_steps, nsb_step_info* log, int max_log, int* s
 int nsb_get_center(nsb_ctx* ctx, double* u_c, double* v_c);
 /* seconds spent inside nsb_sor so far (CUDA events); what main.c:153 prints */
 double nsb_sor_seconds(const nsb_ctx* ctx);
+/* kernels this library has enqueued on the context so far (bench.py's gpu_launches) */
+long long nsb_launch_count(const nsb_ctx* ctx);
 
 /* host <-> HBM.  host holds (i_max+2)*(j_max+2) doubles in the given layout. */
 int nsb_upload(nsb_ctx* ctx, int field, const double* host, int layout);

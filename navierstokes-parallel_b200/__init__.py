@@ -105,6 +105,7 @@ ABI = {
     "nsb_run": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(StepInfo), C.c_int, int_p, dbl_p]),
     "nsb_get_center": (C.c_int, [C.c_void_p, dbl_p, dbl_p]),
     "nsb_sor_seconds": (C.c_double, [C.c_void_p]),
+    "nsb_launch_count": (C.c_longlong, [C.c_void_p]),
     "nsb_upload": (C.c_int, [C.c_void_p, C.c_int, dbl_p, C.c_int]),
     "nsb_download": (C.c_int, [C.c_void_p, C.c_int, dbl_p, C.c_int]),
     "nsb_output": (C.c_int, [C.c_void_p, C.c_double, C.c_char_p]),
@@ -291,6 +292,9 @@ class Solver:
 
     def sor_seconds(self):
         return self._L.nsb_sor_seconds(self._h)
+
+    def launch_count(self):
+        return self._L.nsb_launch_count(self._h)
 
     def output(self, t, prefix):
         self._ck(self._L.nsb_output(self._h, t, os.fsencode(prefix)))

@@ -277,6 +277,8 @@ extern "C" void* nsb_stream(const nsb_ctx* c) { return c ? (void*)c->stream : NU
 
 extern "C" double nsb_sor_seconds(const nsb_ctx* c) { return c ? c->sor_seconds : 0.0; }
 
+extern "C" long long nsb_launch_count(const nsb_ctx* c) { return c ? c->n_launches : 0; }
+
 // u and v at (i, local row l)
 int nsb_get_value(nsb_ctx* c, int i, int l, double* u_c, double* v_c) {
     CU(c, cudaSetDevice(c->device));

@@ -45,12 +45,12 @@ cudaError_t nsb_launch_to_xfast(nsb_ctx* c, const double* src_ref, double* dst) 
     const int nx = c->g.ni + 2, ny = c->g.nj + 2;
     dim3 b(TT, 8), g((ny + TT - 1) / TT, (nx + TT - 1) / TT);
     ref_to_grid_kernel<<<g, b, 0, c->stream>>>(src_ref, dst, c->g.pitch, nx, ny);
-    return cudaGetLastError();
+    return NSB_LAUNCHED(c, 1);
 }
 
 cudaError_t nsb_launch_from_xfast(nsb_ctx* c, const double* src, double* dst_ref) {
     const int nx = c->g.ni + 2, ny = c->g.nj + 2;
     dim3 b(TT, 8), g((nx + TT - 1) / TT, (ny + TT - 1) / TT);
     grid_to_ref_kernel<<<g, b, 0, c->stream>>>(src, dst_ref, c->g.pitch, nx, ny);
-    return cudaGetLastError();
+    return NSB_LAUNCHED(c, 1);
 }

@@ -81,7 +81,7 @@ cudaError_t nsb_launch_set_inflow(nsb_ctx* c, int side, double u_fix, double v_f
     const int n = (side == NSB_TOP || side == NSB_BOTTOM) ? c->g.ni : c->g.nj;
     set_inflow_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(c->u, c->v, c->g.pitch, c->g.ni, c->g.nj,
                                                               side, u_fix, v_fix);
-    return cudaGetLastError();
+    return NSB_LAUNCHED(c, 1);
 }
 
 // ------------------------------------------------------------------ F and G
@@ -162,7 +162,7 @@ cudaError_t nsb_launch_fg(nsb_ctx* c, double dt, double gamma) {
     const int g_hi = c->wall_top ? c->g.nj - 1 : c->g.nj;
     if (c->use_recip) fg_kernel<true><<<g, b, 0, c->stream>>>(c->u, c->v, c->F, c->G, c->g.pitch, c->g.ni, c->g.nj, g_hi, m);
     else fg_kernel<false><<<g, b, 0, c->stream>>>(c->u, c->v, c->F, c->G, c->g.pitch, c->g.ni, c->g.nj, g_hi, m);
-    return cudaGetLastError();
+    return NSB_LAUNCHED(c, 1);
 }
 
 // ------------------------------------------------------------------ RHS (main.c:116-120)
@@ -201,7 +201,7 @@ cudaError_t nsb_launch_rhs(nsb_ctx* c, double dt) {
                     (c->O.div_mode == NSB_DIV_AUTO && pow2(c->dx) && pow2(c->dy));
     if (rd) rhs_kernel<true><<<g, b, 0, c->stream>>>(c->F, c->G, c->rhs, c->g.pitch, c->g.ni, c->g.nj, m);
     else rhs_kernel<false><<<g, b, 0, c->stream>>>(c->F, c->G, c->rhs, c->g.pitch, c->g.ni, c->g.nj, m);
-    return cudaGetLastError();
+    return NSB_LAUNCHED(c, 1);
 }
 
 cudaError_t nsb_launch_fg_rhs(nsb_ctx* c, double dt, double gamma) {
@@ -320,7 +320,7 @@ __global__ void __launch_bounds__(128) red_close_kernel(SlabRed sr, unsigned lon
 
 cudaError_t nsb_launch_red_close(nsb_ctx* c) {
     red_close_kernel<<<1, 128, 0, c->stream>>>(nsb_slab_red(c), c->red_round, c->d_red);
-    return cudaGetLastError();
+    return NSB_LAUNCHED(c, 1);
 }
 
 static void uv_grid(const nsb_ctx* c, dim3& g) {
@@ -351,7 +351,7 @@ cudaError_t nsb_launch_update_uv(nsb_ctx* c, double dt) {
     UvRedArgs ra = uv_red_args(c);
     if (rd) update_uv_kernel<true, true><<<g, 256, 0, c->stream>>>(c->u, c->v, c->F, c->G, p, c->g.pitch, c->g.ni, c->g.nj, m, ra);
     else update_uv_kernel<false, true><<<g, 256, 0, c->stream>>>(c->u, c->v, c->F, c->G, p, c->g.pitch, c->g.ni, c->g.nj, m, ra);
-    return cudaGetLastError();
+    return NSB_LAUNCHED(c, 1);
 }
 
 cudaError_t nsb_launch_reduce_uvp(nsb_ctx* c) {
@@ -360,5 +360,5 @@ cudaError_t nsb_launch_reduce_uvp(nsb_ctx* c) {
     uv_grid(c, g);
     update_uv_kernel<true, false><<<g, 256, 0, c->stream>>>(c->u, c->v, c->F, c->G, c->pbuf[c->pcur], c->g.pitch,
                                                             c->g.ni, c->g.nj, m, uv_red_args(c));
-    return cudaGetLastError();
+    return NSB_LAUNCHED(c, 1);
 }

@@ -162,9 +162,13 @@ struct nsb_ctx {
     double* h_stage; size_t h_stage_elems;   // pinned staging for uploads/downloads
     cudaEvent_t ev0, ev1, ev_chk[2];
     double sor_seconds;
+    long long n_launches;  // kernels of this library enqueued so far (nsb_launch_count)
     int last_sor_engine;
     char err[512];
 };
+
+// every launcher ends with this: counts the kernels it enqueued and returns the launch status
+#define NSB_LAUNCHED(c, n) ((c)->n_launches += (n), cudaGetLastError())
 
 static inline size_t nsb_index(const NsbGrid& g, int i, int j) {
     return (size_t)(j + NSB_ROW0) * (size_t)g.pitch + (size_t)(i + NSB_COL0);

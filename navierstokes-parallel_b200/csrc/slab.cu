@@ -104,7 +104,7 @@ cudaError_t nsb_launch_halo_push(nsb_ctx* c, int kind) {
     }
     if (dn.n == 0 && up.n == 0) return cudaSuccess;
     halo_push_kernel<<<2, 1024, 0, c->stream>>>(dn, up);
-    return cudaGetLastError();
+    return NSB_LAUNCHED(c, 1);
 }
 
 cudaError_t nsb_launch_halo_wait(nsb_ctx* c, int kind) {
@@ -122,7 +122,7 @@ cudaError_t nsb_launch_halo_wait(nsb_ctx* c, int kind) {
     }
     if (!fd && !fu) return cudaSuccess;
     halo_wait_kernel<<<1, 32, 0, c->stream>>>(fd, c->epoch_in[0], fu, c->epoch_in[1], &c->d_sync->error);
-    return cudaGetLastError();
+    return NSB_LAUNCHED(c, 1);
 }
 
 // ------------------------------------------------------------------ wiring

@@ -26,7 +26,7 @@ __global__ void sor_begin_kernel(SorCtl* ctl, const StepRed* red, double eps, lo
 cudaError_t nsb_launch_sor_begin(nsb_ctx* c) {
     sor_begin_kernel<<<1, 32, 0, c->stream>>>(c->d_ctl, c->d_red, c->P.epsilon,
                                               (long long)c->g.ni * (long long)c->J);      // global cell count
-    return cudaGetLastError();
+    return NSB_LAUNCHED(c, 1);
 }
 
 // ---- Neumann ghosts, main.cu:249-273 (corner copies there are racy and never read: skipped)
@@ -133,7 +133,7 @@ cudaError_t nsb_launch_sor_simple_iter(nsb_ctx* c, int it, double* p, int check)
     }
     if (c->use_recip) sor_residual_kernel<true><<<rgrid, 256, 0, c->stream>>>(p, c->rhs, c->g.pitch, ni, nj, k, c->d_partials, c->d_ctl, it, check);
     else sor_residual_kernel<false><<<rgrid, 256, 0, c->stream>>>(p, c->rhs, c->g.pitch, ni, nj, k, c->d_partials, c->d_ctl, it, check);
-    return cudaGetLastError();
+    return NSB_LAUNCHED(c, 5);
 }
 
 // ---- ghosts of the final pressure for the fused engines.  The reference leaves in the ghost
@@ -163,5 +163,5 @@ cudaError_t nsb_launch_sor_finish_ghosts(nsb_ctx* c, double* pfinal, const doubl
     const int n = max(c->g.ni, c->g.nj);
     sor_finish_ghosts_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(pfinal, pprev, c->g.pitch, c->g.ni, c->g.nj,
                                                                      c->wall_bottom ? 1 : 0, c->wall_top ? 1 : 0);
-    return cudaGetLastError();
+    return NSB_LAUNCHED(c, 1);
 }

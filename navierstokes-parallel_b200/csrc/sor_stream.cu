@@ -556,7 +556,7 @@ __global__ void __launch_bounds__(128) sor_close_kernel(SlabRed red, unsigned lo
 cudaError_t nsb_launch_sor_close(nsb_ctx* c, int it, int check) {
     sor_close_kernel<<<1, 128, 0, c->stream>>>(nsb_slab_red(c), c->red_round + (unsigned long long)it, c->d_ctl, it,
                                                (long long)c->g.ni * (long long)c->J, check);
-    return cudaGetLastError();
+    return NSB_LAUNCHED(c, 1);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -653,5 +653,5 @@ cudaError_t nsb_launch_sor_stream_iter(nsb_ctx* c, int it, const double* pin, do
     const int blocks = (a.n_tasks + SOR_WARPS - 1) / SOR_WARPS;
     if (c->use_recip) sor_stream_kernel<true><<<blocks, SOR_THREADS, SOR_SMEM_BYTES, c->stream>>>(a);
     else sor_stream_kernel<false><<<blocks, SOR_THREADS, SOR_SMEM_BYTES, c->stream>>>(a);
-    return cudaGetLastError();
+    return NSB_LAUNCHED(c, 1);
 }
