@@ -57,9 +57,12 @@ enum {
 /* SOR engines */
 enum {
     NSB_SOR_AUTO = 0,
-    NSB_SOR_STREAM = 1,   /* fused red+black+residual streaming pass, one launch per iteration */
+    NSB_SOR_STREAM = 1,   /* fused red+black+residual streaming pass; on a single slab ALL iterations of a
+                             solve run in one persistent launch (tasks of iteration n+1 start as soon as
+                             their neighbours of iteration n are done), on y-slabs one launch per iteration */
     NSB_SOR_RESIDENT = 2, /* grid held on-chip by one thread-block cluster, all iterations in one launch */
-    NSB_SOR_SIMPLE = 3    /* one launch per colour + residual launch (validation kernel)        */
+    NSB_SOR_SIMPLE = 3,   /* one launch per colour + residual launch (validation kernel)        */
+    NSB_SOR_STREAM_LAUNCH = 4 /* the streaming pass with one launch per iteration on a single slab too */
 };
 
 /* io.h:14 init(): the 15 positional values of a parameter file, same order */

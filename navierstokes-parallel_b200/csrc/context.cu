@@ -84,7 +84,9 @@ extern "C" void nsb_destroy(nsb_ctx* c) {
     for (int r = 0; r < c->world && r < NSB_MAX_RANKS; r++)
         if (r != c->rank && c->peer[r].mapped_ipc && c->peer[r].base) cudaIpcCloseMemHandle(c->peer[r].base);
     if (c->arena) cudaFree(c->arena);
-    double* bufs[] = {c->d_partials, c->d_red_partials, c->d_bandvals};
+    double* bufs[] = {c->d_partials, c->d_red_partials, c->d_bandvals, c->d_partials2};
+    if (c->d_claim) cudaFree(c->d_claim);
+    if (c->d_done) cudaFree(c->d_done);
     for (double* b : bufs) if (b) cudaFree(b);
     if (c->d_ctl) cudaFree(c->d_ctl);
     if (c->d_red) cudaFree(c->d_red);
@@ -235,6 +237,12 @@ int nsb_create_slab_internal(const nsb_params* P, const nsb_options* opt, int ra
     int np = c->n_partials;
     if (np < 8 * c->g.nj + 64) np = 8 * c->g.nj + 64;
     CUC(cudaMalloc((void**)&c->d_partials, (size_t)np * sizeof(double)));
+    CUC(cudaMalloc((void**)&c->d_partials2, (size_t)2 * c->n_partials * sizeof(double)));
+    CUC(cudaMalloc((void**)&c->d_claim, 8 * sizeof(unsigned long long)));
+    CUC(cudaMalloc((void**)&c->d_done, (size_t)c->n_partials * sizeof(unsigned long long)));
+    CUC(cudaMemsetAsync(c->d_partials2, 0, (size_t)2 * c->n_partials * sizeof(double), c->stream));
+    CUC(cudaMemsetAsync(c->d_claim, 0, 8 * sizeof(unsigned long long), c->stream));
+    CUC(cudaMemsetAsync(c->d_done, 0, (size_t)c->n_partials * sizeof(unsigned long long), c->stream));
     c->n_red_partials = 3 * 4 * c->g.nj + 64;
     CUC(cudaMalloc((void**)&c->d_red_partials, (size_t)c->n_red_partials * sizeof(double)));
     CUC(cudaMalloc((void**)&c->d_bandvals, (size_t)NSB_RED_Q * (c->n_chunks + 1) * sizeof(double)));
@@ -430,4 +438,29 @@ extern "C" int nsb_output(nsb_ctx* c, double t, const char* prefix) {
     for (int k = 0; k < 3; k++) fclose(fp[k]);
     free(host);
     return rc;
+}
+
+// Developer aid: read the persistent sweep's counters on a side stream while a kernel is running.
+// out[0..7] = claim counter + tickets, out[8] = ctl.iters, out[9] = ctl.converged, out[10] = wait-error flag,
+// out[11] = smallest done flag, out[12] = largest done flag.
+extern "C" int nsb_debug_peek(nsb_ctx* c, unsigned long long* out) {
+    if (!c || !out) return NSB_ERR_ARG;
+    cudaStream_t st;
+    if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) return NSB_ERR_CUDA;
+    SorCtl k; int err = 0;
+    unsigned long long* done = (unsigned long long*)malloc((size_t)c->n_partials * 8);
+    cudaMemcpyAsync(out, c->d_claim, 64, cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(&k, c->d_ctl, sizeof k, cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(&err, &c->d_sync->error, 4, cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(done, c->d_done, (size_t)c->n_partials * 8, cudaMemcpyDeviceToHost, st);
+    cudaError_t e = cudaStreamSynchronize(st);
+    cudaStreamDestroy(st);
+    out[8] = (unsigned long long)k.iters; out[9] = (unsigned long long)k.converged; out[10] = (unsigned long long)err;
+    unsigned long long lo = ~0ull, hi = 0;
+    for (int i = 0; i < c->n_partials; i++) { if (done[i] < lo) lo = done[i]; if (done[i] > hi) hi = done[i]; }
+    out[11] = lo; out[12] = hi; out[13] = c->flag_base; out[14] = (unsigned long long)c->n_partials;
+    int nlo = 0; for (int i = 0; i < c->n_partials; i++) if (done[i] == lo) nlo++;
+    out[15] = (unsigned long long)nlo;
+    free(done);
+    return e == cudaSuccess ? NSB_OK : NSB_ERR_CUDA;
 }

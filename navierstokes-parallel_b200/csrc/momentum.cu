@@ -246,14 +246,19 @@ __global__ void __launch_bounds__(256) update_uv_kernel(double* __restrict__ u, 
         const double pc = p[o];
         double un, vn;
         if (UPDATE) {
-            un = u[o]; vn = v[o];
+            // u, v are only READ where the update does not reach (last column / last row): the rest
+            // of the pass reads F, G, p and writes u, v -- 40 B per cell
             if (i <= ni - 1) {
                 un = __dsub_rn(F[o], __dmul_rn(m.dt, nsb_div<RECIPD>(__dsub_rn(p[o + 1], pc), m.dx, m.rdx)));
                 u[o] = un;
+            } else {
+                un = u[o];
             }
             if (j <= ra.v_hi) {                                  // global j <= j_max-1 (main.c:134)
                 vn = __dsub_rn(G[o], __dmul_rn(m.dt, nsb_div<RECIPD>(__dsub_rn(p[o + pitch], pc), m.dy, m.rdy)));
                 v[o] = vn;
+            } else {
+                vn = v[o];
             }
         } else {
             un = u[o]; vn = v[o];

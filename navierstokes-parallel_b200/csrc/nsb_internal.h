@@ -153,6 +153,10 @@ struct nsb_ctx {
     // SOR machinery
     SorCtl* d_ctl; SorCtl* h_ctl;       // device / pinned host
     double* d_partials; int n_partials;
+    // persistent multi-iteration sweep (sor_stream.cu): claim counter + 4 iteration tickets, one
+    // "done" flag per task, double-buffered partials, epoch base of the flags
+    unsigned long long* d_claim; unsigned long long* d_done; double* d_partials2;
+    unsigned long long flag_base;
     int chunk_rows, n_strips, n_chunks;
     // step reductions
     StepRed* d_red; StepRed* h_red;
@@ -183,6 +187,8 @@ cudaError_t nsb_launch_update_uv(nsb_ctx* c, double dt);
 cudaError_t nsb_launch_reduce_uvp(nsb_ctx* c);     // max u, max v, sum p^2 without updating
 cudaError_t nsb_launch_sor_begin(nsb_ctx* c);      // threshold from sum p^2, clears the flags
 cudaError_t nsb_launch_sor_stream_iter(nsb_ctx* c, int it, const double* pin, double* pout, int check);
+int nsb_sor_persist_supported(const nsb_ctx* c);
+cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int n_iter, int check);   // all iterations, one launch
 cudaError_t nsb_launch_sor_simple_iter(nsb_ctx* c, int it, double* p, int check);
 cudaError_t nsb_launch_sor_finish_ghosts(nsb_ctx* c, double* pfinal, const double* pprev);
 cudaError_t nsb_launch_to_xfast(nsb_ctx* c, const double* src_ref, double* dst);   // [i][j] -> grid

@@ -122,8 +122,9 @@ __device__ __forceinline__ void sor_close_iteration(double total, SorCtl* ctl, i
     double res = sqrt(total / (double)cells);              // main.cu:588
     ctl->sum_r2 = total;
     ctl->res = res;
-    ctl->iters = it + 1;
     if (res <= ctl->thresh) ctl->converged = 1;             // main.cu:713
+    __threadfence();                                        // `converged` is visible before `iters` says "closed"
+    *((volatile int*)&ctl->iters) = it + 1;
     __threadfence();
     sor_publish(ctl);
 }
@@ -169,6 +170,8 @@ struct TaskCtx {
     uint32_t bar_base;        // this warp's mbarriers (shared address): NST FULL, then NST EMPTY
     int lane;
     uint32_t zero;            // run-time 0 (see the EMPTY-barrier arrive)
+    uint32_t full_par, empty_par;   // phase parities the barriers start this task with (persistent sweep: the
+                                    // barriers live across tasks; 0 in the one-task-per-warp kernel)
     // producer state (warp-uniform)
     const double* pin_next;   // first row of the next pair to fetch, first column of the strip
     const double* rhs_next;
@@ -235,7 +238,7 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
     {
         const uint32_t ph = ((uint32_t)(sb + S) >> (1 + SOR_LOG_NST)) & 1u;   // use count of the stage, mod 2
         if ((S & 1) == 0) {
-            mbar_wait(t.bar_base + st * 8, ph);
+            mbar_wait(t.bar_base + st * 8, ph ^ t.full_par);
 #ifdef SOR_SYNC_EACH_STEP
             __syncwarp();
 #endif
@@ -258,7 +261,7 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
                             (__double2hiint(d.x) ^ __double2hiint(P[sD][0]) ^ __double2hiint(P[sD][2])) ^
                             (__double2hiint(R[sD][0]) ^ __double2hiint(R[sD][2]));
             mbar_arrive(t.bar_base + (SOR_NST + st) * 8 + ((uint32_t)dep & t.zero));
-            issue_pair(t, st, ph, true);
+            issue_pair(t, st, ph ^ t.empty_par, true);
         }
     }
 
@@ -318,12 +321,36 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
         const double u1 = sor_cell<RECIP>(X[k1], e1, w1, P[sD][k1], P[sB][k1], R[sC][k1], kf);
         if (row_in && (!EX || lg.inner[k0])) X[k0] = u0;
         if (row_in && (!EX || lg.inner[k1])) X[k1] = u1;
+        if (EX && (!EY || (r >= t.jc0 && r <= t.jc1))) {
+            // ghost columns of the final row, as the refresh before colour 1 left them (main.cu:694):
+            // the west ghost lives in the halo lane 0 of the first strip, the east ghost in an owner
+            // lane (stored below with its group) or in the halo lane 31 of the last strip
+            if (lg.ghostW) t.pout_row[3] = X[3];
+            if (lg.kGhostE >= 0 && !lg.owner && t.lane == 31) {
+                if (lg.kGhostE == 0) t.pout_row[0] = X[0];
+                else if (lg.kGhostE == 1) t.pout_row[1] = X[1];
+                else if (lg.kGhostE == 2) t.pout_row[2] = X[2];
+                else t.pout_row[3] = X[3];
+            }
+        }
         // row j-2 is final: store it (one full 32-byte sector per lane)
         if (lg.owner && (!EY || (r >= t.jc0 && r <= t.jc1))) {
             double2* q = reinterpret_cast<double2*>(t.pout_row);
             q[0] = make_double2(X[0], X[1]);
             q[1] = make_double2(X[2], X[3]);
             if (EY) {
+                // ghost rows j = 0 / j_max+1 as the same refresh left them (copies of row 1 / j_max taken
+                // before the black update, held in the window slots B / D)
+                if (r == 1 && t.wall_bottom) {
+                    double2* h = reinterpret_cast<double2*>(t.pout_row - t.pitch);
+                    h[0] = make_double2(P[sB][0], P[sB][1]);
+                    h[1] = make_double2(P[sB][2], P[sB][3]);
+                }
+                if (r == t.nj && t.wall_top) {
+                    double2* h = reinterpret_cast<double2*>(t.pout_row + t.pitch);
+                    h[0] = make_double2(P[sD][0], P[sD][1]);
+                    h[1] = make_double2(P[sD][2], P[sD][3]);
+                }
                 // y-slab halo: the three rows next to a slab boundary also go straight into the
                 // neighbour's halo rows over NVLink (peer store), SURVEY 8e
                 if (t.push_down && r <= 3) {
@@ -456,6 +483,7 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
         t.pitch = a.pitch;
         t.lane = lane;
         t.zero = a.zero;
+        t.full_par = 0u; t.empty_par = 0u;
         const long long coff = (long long)g0 * NSB_GROUP;    // first column of the strip
         const long long row_first = (long long)(t.jstart + NSB_ROW0) * a.pitch;
         t.pin_next = a.pin + row_first + coff;
@@ -541,6 +569,226 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
             if (threadIdx.x == 0) sor_close_iteration(sh[0], a.ctl, a.it, a.k.cells);
         }
     }
+}
+
+// ------------------------------------------------------------------------------------------
+// Persistent multi-iteration sweep (single slab): ALL iterations of a solve in one launch.
+//
+// Why: one launch per iteration costs a pipeline drain per iteration -- a task (one warp marching up
+// 126 rows) lives ~100-150 us, so the last round of blocks leaves most SMs idle; measured launch time
+// = 75 us + 4.03 us per 120-row band at 8192 columns (profiles/r1d_wave_probe.txt), i.e. 22 % of a
+// launch at 8192^2 is drain.  Here the warps of a fixed grid claim tasks from one global counter,
+// task id = iteration * n_tasks + (chunk * n_strips + strip), and a task of iteration n starts as
+// soon as its 3 x 3 neighbourhood of tasks of iteration n-1 is done (their rows are what it reads,
+// and they are the only readers of the rows it overwrites in the ping-pong buffer), so the sweep
+// of iteration n+1 follows the sweep of iteration n up the grid without a global barrier.
+//   - deadlock freedom: ids are claimed in order and a task only waits for smaller ids, which are
+//     running on resident warps or finished; every wait still has a deadline (slab.cuh);
+//   - residual: per-task partials (double-buffered by iteration parity), the warp that takes the
+//     last ticket of an iteration sums them in the same fixed order as the one-launch-per-iteration
+//     kernel (same bits), closes the iteration and publishes the control block;
+//   - convergence: a task of iteration n waits until iteration n-2 is closed and stops if that or an
+//     earlier one converged.  Tasks of iteration m+1 may run after iteration m converged: they write
+//     the OTHER ping-pong buffer, the converged iterate stays intact (same contract as the queued
+//     launches of the per-iteration kernel).
+struct SorPersistArgs {
+    SorStreamArgs s;                 // geometry, coefficients, ctl; pin / pout = buffers of iteration 0
+    int n_iter;
+    unsigned long long* claim;       // [0] task counter, [1..4] tickets of iterations mod 4
+    unsigned long long* done;        // [n_tasks] epoch of the last iteration the task finished
+    unsigned long long flag_base;    // epoch of "before iteration 0 of this launch"
+    double* partials2;               // [2][n_tasks]
+};
+
+__device__ __forceinline__ unsigned long long ld_acquire_gpu(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_gpu_s32(const int* p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// one lane: wait until *flag >= want (device scope); false on timeout
+__device__ __forceinline__ bool spin_gpu_ge(const unsigned long long* flag, unsigned long long want, int* err) {
+    if (ld_acquire_gpu(flag) >= want) return true;
+    const unsigned long long t0 = global_timer_ns();
+    while (ld_acquire_gpu(flag) < want) {
+        if (*((volatile int*)err)) return false;
+        if (global_timer_ns() - t0 > NSB_SPIN_TIMEOUT_NS) { *((volatile int*)err) = 1; return false; }
+        __nanosleep(64);
+    }
+    return true;
+}
+
+template <bool RECIP>
+__global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const SorStreamArgs& a = pa.s;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned FULLM = 0xffffffffu;
+    const unsigned long long total = (unsigned long long)pa.n_iter * (unsigned long long)a.n_tasks;
+    unsigned char* ring = smem_raw + warp * SOR_WARP_SMEM;
+    const uint32_t bar_base = smem_u32(smem_raw + SOR_WARPS * SOR_WARP_SMEM + warp * 2 * SOR_NST * 8);
+    // The mbarriers are initialised once and live across the tasks of this warp.  Per task and stage
+    // the FULL barrier completes (pairs per stage + 1) phases (the last re-arm is never waited for, it
+    // is a plain arrive), the EMPTY barrier (pairs per stage): the parities a task starts with follow.
+    uint32_t full_par = 0u, empty_par = 0u;
+    if (lane == 0) {
+#pragma unroll
+        for (int q = 0; q < 2 * SOR_NST; q++) mbar_init(bar_base + q * 8, q < SOR_NST ? 1u : 32u);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncwarp();
+
+    for (;;) {
+        unsigned long long id = 0;
+        if (lane == 0) id = atomicAdd(pa.claim, 1ull);
+        id = __shfl_sync(FULLM, id, 0);
+        if (id >= total) break;
+        const int it = (int)(id / (unsigned long long)a.n_tasks);
+        const int task = (int)(id - (unsigned long long)it * (unsigned long long)a.n_tasks);
+        const int strip = task % a.n_strips;
+        const int chunk = task / a.n_strips;
+
+        // ---- may this iteration run?  iteration it-2 must be closed, and nothing before may have converged
+        // (the wait also keeps the double-buffered partials and the 4 tickets of iteration it-2 / it-4 safe,
+        //  so it does not depend on `check`)
+        int stop = 0;
+        {
+            if (lane == 0) {
+                if (it >= 2) {
+                    const unsigned long long t0 = global_timer_ns();
+                    while (ld_acquire_gpu_s32(&a.ctl->iters) < a.it + it - 1) {
+                        if (a.check && ld_acquire_gpu_s32(&a.ctl->converged)) break;   // nothing closes after convergence
+                        if (*((volatile int*)a.err) || global_timer_ns() - t0 > NSB_SPIN_TIMEOUT_NS) { *((volatile int*)a.err) = 1; stop = 1; break; }
+                        __nanosleep(64);
+                    }
+                }
+                if (a.check && ld_acquire_gpu_s32(&a.ctl->converged)) stop = 1;
+            }
+            stop = __shfl_sync(FULLM, stop, 0);
+        }
+        if (stop) break;
+
+        // ---- wait for the 3 x 3 neighbourhood of the previous iteration
+        if (it > 0) {
+            int ok = 1;
+            if (lane < 9) {
+                const int cc = chunk + lane / 3 - 1, ss = strip + lane % 3 - 1;
+                if (cc >= 0 && cc < a.n_chunks && ss >= 0 && ss < a.n_strips)
+                    ok = spin_gpu_ge(pa.done + (size_t)cc * a.n_strips + ss, pa.flag_base + (unsigned long long)it, a.err) ? 1 : 0;
+            }
+            ok = __all_sync(FULLM, ok);
+            if (!ok) break;
+            asm volatile("fence.proxy.async;" ::: "memory");   // other warps' generic stores -> this warp's TMA reads
+        }
+
+        const double* pin = (it & 1) ? a.pout : a.pin;
+        double* pout = (it & 1) ? const_cast<double*>(a.pin) : a.pout;
+
+        const int g0 = strip * NSB_STRIP_GROUPS;
+        const int g = g0 + lane;
+        const int i0 = g * NSB_GROUP - NSB_COL0;
+        LaneGeom lg;
+        bool all_inner = (g < a.n_groups);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            lg.inner[k] = (i0 + k >= 1) && (i0 + k <= a.ni);
+            all_inner = all_inner && lg.inner[k];
+        }
+        lg.owner = (g < a.n_groups) && lane >= 1 && lane <= NSB_STRIP_GROUPS;
+        lg.ghostW = (i0 + 3 == 0);
+        const int kg = a.ni + 1 - i0;
+        lg.kGhostE = (kg >= 0 && kg <= 3) ? kg : -1;
+        lg.warpW = __any_sync(FULLM, lg.ghostW);
+        lg.warpE = __any_sync(FULLM, lg.kGhostE >= 0);
+        const bool edge_strip = !__all_sync(FULLM, all_inner);
+
+        TaskCtx t;
+        t.jc0 = 1 + chunk * a.chunk_rows;
+        t.jc1 = min(t.jc0 + a.chunk_rows - 1, a.nj);
+        t.jstart = t.jc0 - 3;
+        t.nj = a.nj;
+        t.wall_bottom = true; t.wall_top = true;
+        t.rlo = 1; t.rhi = a.nj;
+        t.push_down = false; t.push_up = false;
+        t.pitch = a.pitch;
+        t.lane = lane;
+        t.zero = a.zero;
+        const long long coff = (long long)g0 * NSB_GROUP;
+        const long long row_first = (long long)(t.jstart + NSB_ROW0) * a.pitch;
+        t.pin_next = pin + row_first + coff;
+        t.rhs_next = a.rhs + row_first + coff;
+        t.j_next = t.jstart;
+        t.j_limit = min(t.jc1 + 3, a.nj + 3);
+        t.pout_row = pout + row_first - 2 * a.pitch + coff + (long long)lane * NSB_GROUP;
+        t.down_col = pout; t.up_col = pout; t.down_nj = 0;
+        const int groups_here = min(32, a.n_groups - g0);
+        t.copy_bytes = (uint32_t)groups_here * 32u;
+        t.lds_lane = reinterpret_cast<const double*>(ring) + lane * NSB_GROUP;
+        t.smem_base = smem_u32(ring);
+        t.bar_base = bar_base;
+
+        t.full_par = full_par; t.empty_par = empty_par;
+        {
+            const int n_steps = t.jc1 + 3 - t.jstart + 1;
+            const uint32_t pairs_per_stage = (uint32_t)(((n_steps + 7) / 8) * 4 / SOR_NST);
+            full_par ^= (pairs_per_stage + 1u) & 1u;
+            empty_par ^= pairs_per_stage & 1u;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < SOR_NST; q++) issue_pair(t, q, 0u, false);
+
+        double acc;
+        if (edge_strip) acc = sor_run_task<RECIP, true>(t, a.k, lg);
+        else acc = sor_run_task<RECIP, false>(t, a.k, lg);
+        acc = warp_sum(acc);
+        double* part = pa.partials2 + (size_t)(it & 1) * a.n_tasks;
+        if (lane == 0) part[task] = acc;
+
+        // ---- publish: rows and partial are out
+        __threadfence();
+        __syncwarp();
+        unsigned long long tk = 0;
+        if (lane == 0) {
+            st_release_gpu(pa.done + task, pa.flag_base + (unsigned long long)it + 1ull);
+            tk = atomicAdd(pa.claim + 1 + (it & 3), 1ull);
+        }
+        tk = __shfl_sync(FULLM, tk, 0);
+        if (tk == (unsigned long long)a.n_tasks - 1ull) {
+            // this warp closes iteration `it`: band sums in the fixed order of the per-iteration kernel
+            __threadfence();
+            if (lane == 0) pa.claim[1 + (it & 3)] = 0ull;
+            for (int b = 0; b < a.n_chunks; b++) {
+                const double v = warp_ordered_sum(part + (size_t)b * a.n_strips, a.n_strips, lane);
+                if (lane == 0) a.bandvals[b] = v;
+            }
+            __threadfence();
+            __syncwarp();
+            const double tot = warp_ordered_sum(a.bandvals, a.n_chunks, lane);
+            if (lane == 0) {
+                // iterations close in order; nothing closes after the one that converged
+                const unsigned long long t0 = global_timer_ns();
+                while (ld_acquire_gpu_s32(&a.ctl->iters) < a.it + it) {
+                    if (global_timer_ns() - t0 > NSB_SPIN_TIMEOUT_NS) { *((volatile int*)a.err) = 1; break; }
+                    __nanosleep(64);
+                }
+                if (!(a.check && ld_acquire_gpu_s32(&a.ctl->converged))) sor_close_iteration(tot, a.ctl, a.it + it, a.k.cells);
+            }
+            __syncwarp();
+        }
+    }
+}
+
+int nsb_sor_persist_supported(const nsb_ctx* c) {
+    return c->world == 1 && c->chunk_rows >= 4;
 }
 
 // world > 1: the closing of an iteration is its own one-block kernel, so that the sweep kernel never
@@ -653,5 +901,52 @@ cudaError_t nsb_launch_sor_stream_iter(nsb_ctx* c, int it, const double* pin, do
     const int blocks = (a.n_tasks + SOR_WARPS - 1) / SOR_WARPS;
     if (c->use_recip) sor_stream_kernel<true><<<blocks, SOR_THREADS, SOR_SMEM_BYTES, c->stream>>>(a);
     else sor_stream_kernel<false><<<blocks, SOR_THREADS, SOR_SMEM_BYTES, c->stream>>>(a);
+    return NSB_LAUNCHED(c, 1);
+}
+
+// All `n_iter` iterations of a solve in one launch (single slab).  Iteration 0 reads pbuf[pcur].
+cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int n_iter, int check) {
+    if (n_iter <= 0) return cudaSuccess;
+    SorPersistArgs pa;
+    memset(&pa, 0, sizeof pa);
+    SorStreamArgs& a = pa.s;
+    a.pin = c->pbuf[c->pcur]; a.pout = c->pbuf[c->pcur ^ 1]; a.rhs = c->rhs;
+    a.pitch = c->g.pitch; a.ni = c->g.ni; a.nj = c->g.nj;
+    a.chunk_rows = c->chunk_rows; a.n_strips = c->n_strips; a.n_tasks = c->n_partials; a.n_chunks = c->n_chunks;
+    a.n_groups = (int)(c->g.pitch / NSB_GROUP);
+    a.it = 0; a.check = check; a.zero = 0u;
+    const double dx2 = c->dx * c->dx, dy2 = c->dy * c->dy;
+    a.k.om1 = 1.0 - c->P.omega;
+    a.k.w = c->P.omega / (2.0 * (1.0 / dx2 + 1.0 / dy2));
+    a.k.dx2 = dx2; a.k.dy2 = dy2; a.k.rdx2 = 1.0 / dx2; a.k.rdy2 = 1.0 / dy2;
+    a.k.inv_cells_unused = 0.0;
+    a.k.cells = (long long)c->g.ni * (long long)c->J;
+    a.partials = c->d_partials; a.bandvals = c->d_bandvals; a.ctl = c->d_ctl;
+    a.world = 1; a.wall_bottom = 1; a.wall_top = 1;
+    a.err = &c->d_sync->error;
+    pa.n_iter = n_iter;
+    pa.claim = c->d_claim; pa.done = c->d_done; pa.partials2 = c->d_partials2;
+    pa.flag_base = c->flag_base;
+    c->flag_base += (unsigned long long)n_iter + 1ull;
+    static int attr_done = 0;
+    if (!attr_done) {
+        cudaFuncSetAttribute(sor_persist_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES);
+        cudaFuncSetAttribute(sor_persist_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES);
+        attr_done = 1;
+    }
+    int bps = 0;
+    if (c->use_recip) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sor_persist_kernel<true>, SOR_THREADS, SOR_SMEM_BYTES);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sor_persist_kernel<false>, SOR_THREADS, SOR_SMEM_BYTES);
+    if (bps < 1) bps = 1;
+    const long long want = ((long long)n_iter * a.n_tasks + SOR_WARPS - 1) / SOR_WARPS;
+    long long blocks = (long long)c->sm_count * bps;
+    if (blocks > want) blocks = want;
+    // at most two iterations are in flight at any time: more warps than that would only poll flags
+    const long long useful = (2LL * a.n_tasks + SOR_WARPS - 1) / SOR_WARPS + 1;
+    if (blocks > useful) blocks = useful;
+    cudaError_t e = cudaMemsetAsync(c->d_claim, 0, 8 * sizeof(unsigned long long), c->stream);
+    if (e != cudaSuccess) return e;
+    if (c->use_recip) sor_persist_kernel<true><<<(int)blocks, SOR_THREADS, SOR_SMEM_BYTES, c->stream>>>(pa);
+    else sor_persist_kernel<false><<<(int)blocks, SOR_THREADS, SOR_SMEM_BYTES, c->stream>>>(pa);
     return NSB_LAUNCHED(c, 1);
 }

@@ -151,9 +151,10 @@ static int pick_engine(const nsb_ctx* c) {
         const char* env = getenv("NSB_SOR_ENGINE");
         if (env) e = atoi(env);
     }
-    if (c->world > 1) return NSB_SOR_STREAM;                   // the only slab-aware engine
+    if (c->world > 1) return NSB_SOR_STREAM_LAUNCH;            // the only slab-aware engine
     if (e == NSB_SOR_AUTO) e = nsb_sor_resident_supported(c) ? NSB_SOR_RESIDENT : NSB_SOR_STREAM;
     if (e == NSB_SOR_RESIDENT && !nsb_sor_resident_supported(c)) e = NSB_SOR_STREAM;
+    if (e == NSB_SOR_STREAM && !nsb_sor_persist_supported(c)) e = NSB_SOR_STREAM_LAUNCH;
     return e;
 }
 
@@ -176,6 +177,11 @@ static int sor_iterate(nsb_ctx** cs, int n, int max_it, int check) {
         CU(c0, nsb_launch_sor_resident(c0, max_it, check));
         return NSB_OK;
     }
+    if (engine == NSB_SOR_STREAM) {                            // single slab: every iteration in one launch
+        CU(c0, cudaSetDevice(c0->device));
+        CU(c0, nsb_launch_sor_persist(c0, max_it, check));
+        return NSB_OK;
+    }
     const int depth = c0->O.sor_check_batch > 0 ? c0->O.sor_check_batch : 24;
     volatile SorCtl* hv = c0->h_ctl;                           // written by the device (zero-copy)
     int queued = 0;
@@ -183,7 +189,7 @@ static int sor_iterate(nsb_ctx** cs, int n, int max_it, int check) {
         for (int r = 0; r < n; r++) {
             nsb_ctx* c = cs[r];
             if (n > 1) CU(c, cudaSetDevice(c->device));
-            if (engine == NSB_SOR_STREAM)
+            if (engine == NSB_SOR_STREAM_LAUNCH)
                 CU(c, nsb_launch_sor_stream_iter(c, queued, c->pbuf[(c->pcur + queued) & 1],
                                                  c->pbuf[(c->pcur + queued + 1) & 1], check));
             else
@@ -212,10 +218,19 @@ int nsb_ph_sor_end(nsb_ctx* c, int unused) {
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaStreamSynchronize(c->stream));
     CU(c, cudaMemcpy(&c->h_ctl[1], c->d_ctl, sizeof(SorCtl), cudaMemcpyDeviceToHost));
+    {
+        int werr = 0;
+        CU(c, cudaMemcpy(&werr, &c->d_sync->error, sizeof werr, cudaMemcpyDeviceToHost));
+        if (werr) return nsb_fail(c, NSB_ERR_CUDA, "SOR: a wait inside the sweep kernel timed out (rank %d)", c->rank);
+    }
     const int iters = c->h_ctl[1].iters;
-    if (c->last_sor_engine == NSB_SOR_STREAM) {
+    if (c->last_sor_engine == NSB_SOR_STREAM || c->last_sor_engine == NSB_SOR_STREAM_LAUNCH) {
         c->pcur = (c->pcur + iters) & 1;
-        if (iters > 0) CU(c, nsb_launch_sor_finish_ghosts(c, c->pbuf[c->pcur], c->pbuf[c->pcur ^ 1]));
+        // per-launch sweeps: the other buffer still holds the previous iterate, which the ghost
+        // fix-up reads.  The persistent sweep stores the ghost cells itself (iterations that ran past
+        // the converged one may have overwritten the other buffer).
+        if (iters > 0 && c->last_sor_engine == NSB_SOR_STREAM_LAUNCH)
+            CU(c, nsb_launch_sor_finish_ghosts(c, c->pbuf[c->pcur], c->pbuf[c->pcur ^ 1]));
     }
     c->seq += (unsigned long long)iters;
     c->red_round += (unsigned long long)iters;

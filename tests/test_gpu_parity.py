@@ -98,14 +98,14 @@ def test_layout_roundtrip_both_layouts():
 SOR_SHAPES = [(8, 8), (16, 16), (31, 17), (120, 40), (121, 33), (257, 64), (64, 300), (500, 7), (3, 3), (1, 9), (9, 1)]
 
 
-@pytest.mark.parametrize("engine", ["stream", "simple"])
+@pytest.mark.parametrize("engine", ["stream", "launch", "simple"])
 @pytest.mark.parametrize("ni,nj", SOR_SHAPES)
 def test_sor_per_iteration_bit_exact(engine, ni, nj):
     """p after 1, 2, 3, +5 iterations equals the oracle's red-black iterate bit for bit, residual
     norm to 1e-12 relative; sizes include non-multiples of every tile dimension (the reference's
     CUDA kernel is wrong for those)."""
     m = nsb()
-    eng = dict(stream=m.SOR_STREAM, simple=m.SOR_SIMPLE)[engine]
+    eng = dict(stream=m.SOR_STREAM, launch=m.SOR_STREAM_LAUNCH, simple=m.SOR_SIMPLE)[engine]
     a, b = 1.0, 0.9
     s, P = _solver(m, engine=eng, i_max=ni, j_max=nj, a=a, b=b, omega=1.7)
     L = ob.lib()
@@ -147,12 +147,12 @@ def test_sor_division_modes(div_mode):
     s.close()
 
 
-@pytest.mark.parametrize("engine", ["stream", "simple"])
+@pytest.mark.parametrize("engine", ["stream", "launch", "simple"])
 def test_sor_convergence_iteration_count(engine):
     """Converged solve: same iteration count, same return value (it+1), bit-equal p; then the
     not-converged contract (-1, p = last iterate)."""
     m = nsb()
-    eng = dict(stream=m.SOR_STREAM, simple=m.SOR_SIMPLE)[engine]
+    eng = dict(stream=m.SOR_STREAM, launch=m.SOR_STREAM_LAUNCH, simple=m.SOR_SIMPLE)[engine]
     ni, nj = 48, 40
     s, P = _solver(m, engine=eng, i_max=ni, j_max=nj, epsilon=1e-5, max_it=5000)
     p = np.zeros(s.shape)
@@ -201,10 +201,10 @@ def _compare_run(m, c, engine):
     s.close()
 
 
-@pytest.mark.parametrize("engine", ["stream", "simple"])
+@pytest.mark.parametrize("engine", ["stream", "launch", "simple"])
 def test_whole_run_matches_committed_redblack_fixtures(engine):
     m = nsb()
-    eng = dict(stream=m.SOR_STREAM, simple=m.SOR_SIMPLE)[engine]
+    eng = dict(stream=m.SOR_STREAM, launch=m.SOR_STREAM_LAUNCH, simple=m.SOR_SIMPLE)[engine]
     cases = [c for c in json.load(open(os.path.join(GOLD, "runs.json"))) if c["sor_order"] == 1]
     assert len(cases) >= 4
     for c in cases:
@@ -259,14 +259,15 @@ def test_stream_engine_equals_simple_engine_at_scale():
     m = nsb()
     ni, nj = 2048, 1536
     outs = []
-    for eng in (m.SOR_STREAM, m.SOR_SIMPLE):
+    for eng in (m.SOR_STREAM, m.SOR_STREAM_LAUNCH, m.SOR_SIMPLE):
         s, P = _solver(m, engine=eng, i_max=ni, j_max=nj)
         s.upload(m.P, _rand(s.shape, 31)); s.upload(m.RHS, _rand(s.shape, 32))
         r = s.sor_iterations(7)
         outs.append((s.download(m.P)[1:-1, 1:-1], r))
         s.close()
-    assert np.array_equal(outs[0][0], outs[1][0])
-    assert abs(outs[0][1] - outs[1][1]) <= 1e-12 * outs[1][1]
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][0], outs[2][0])
+    assert outs[0][1] == outs[1][1], "persistent and per-launch sweeps must sum the residual in the same order"
+    assert abs(outs[0][1] - outs[2][1]) <= 1e-12 * outs[2][1]
 
 
 def test_stream_engine_is_race_free_over_repeated_runs():
@@ -281,14 +282,15 @@ def test_stream_engine_is_race_free_over_repeated_runs():
     s.sor_iterations(3)
     want = s.download(m.P)[1:-1, 1:-1]
     s.close()
-    for chunk in (0, 16):
-        for rep in range(10):
-            s, P = _solver(m, engine=m.SOR_STREAM, i_max=ni, j_max=nj, chunk_rows=chunk)
-            s.upload(m.P, p0); s.upload(m.RHS, r0)
-            s.sor_iterations(3)
-            got = s.download(m.P)[1:-1, 1:-1]
-            s.close()
-            assert np.array_equal(got, want), f"run {rep} (chunk_rows={chunk}) differs in {(got != want).sum()} cells"
+    for eng in (m.SOR_STREAM, m.SOR_STREAM_LAUNCH):
+        for chunk in (0, 16):
+            for rep in range(10):
+                s, P = _solver(m, engine=eng, i_max=ni, j_max=nj, chunk_rows=chunk)
+                s.upload(m.P, p0); s.upload(m.RHS, r0)
+                s.sor_iterations(3)
+                got = s.download(m.P)[1:-1, 1:-1]
+                s.close()
+                assert np.array_equal(got, want), f"engine {eng} run {rep} (chunk_rows={chunk}) differs in {(got != want).sum()} cells"
 
 
 def test_sor_linearity_and_constant_nullspace():
