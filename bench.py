@@ -271,12 +271,14 @@ def main():
         traffic = json.load(open(os.path.join(ROOT, "profiles", "sor_stream_traffic.json"))).get("dram_bytes_per_launch")
     except Exception:
         pass
-    roofline = {"bound": "hbm", "kernel": "sor_stream_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": "sor_persist_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic if (world == 1 and size == 8192) else None,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
-                "algorithmic_bytes_per_launch": 24.0 * cells_local, "launch_ms": k_ms,
+                "iterations_per_launch": n_k, "algorithmic_bytes_per_launch": 24.0 * cells_local * n_k,
+                "launch_ms": k_ms * n_k, "ms_per_iteration": k_ms,
                 "kernel_mlups": cells_local / (k_ms * 1e-3) / 1e6,
-                "note": "per GPU: one launch = one red+black+residual iteration over this GPU's cells, 24 B per cell"}
+                "note": "per GPU: one launch = %d red+black+residual iterations over this GPU's cells "
+                        "(persistent sweep), 24 B per cell per iteration; traffic = ncu DRAM bytes per iteration" % n_k}
 
     # ---- end to end: host grids in, host grids out, pinned host memory, copies inside the timed region
     e2e = None

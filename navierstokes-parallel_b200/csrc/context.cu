@@ -206,7 +206,7 @@ int nsb_create_slab_internal(const nsb_params* P, const nsb_options* opt, int ra
     const size_t off_scratch = off; off += gbytes;
     d.off_sync = off; off += align_up(sizeof(SlabSync), 256);
     d.off_sorflag = off; off += align_up((size_t)2 * c->n_strips * sizeof(unsigned long long), 256);
-    d.off_gband = off; off += align_up((size_t)2 * NSB_RED_Q * c->nbands_global * sizeof(double), 256);
+    d.off_gband = off; off += align_up((size_t)NSB_RED_DEPTH * NSB_RED_Q * c->nbands_global * sizeof(double), 256);
     c->arena_bytes = off;
     CUC(cudaMalloc((void**)&c->arena, c->arena_bytes));
     CUC(cudaMemsetAsync(c->arena, 0, c->arena_bytes, c->stream));   // calloc semantics, memory.c:3-26
@@ -223,6 +223,7 @@ int nsb_create_slab_internal(const nsb_params* P, const nsb_options* opt, int ra
     d.device = c->device; d.rank = rank; d.world = world; d.nj = c->g.nj; d.j_lo = c->j_lo;
     d.n_strips = c->n_strips; d.nbands_global = c->nbands_global; d.band0 = c->band0;
     d.pitch = c->g.pitch; d.arena_bytes = (long long)c->arena_bytes;
+    memcpy(d.uuid, &prop.uuid, 16);
     if (world > 1) {
         cudaIpcMemHandle_t h;
         CUC(cudaIpcGetMemHandle(&h, c->arena));

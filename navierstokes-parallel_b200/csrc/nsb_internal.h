@@ -83,6 +83,7 @@ struct StepRed {
 // (one IPC handle); peers address it through the offsets of NsbSlabDesc.
 #define NSB_MAX_RANKS 16
 #define NSB_RED_Q 3                  // quantities per reduction round (u max, v max, sum) / (sum r^2)
+#define NSB_RED_DEPTH 4              // gather buffers (round & 3): a rank may run two rounds ahead of a slow reader
 
 struct SlabSync {                    // in the arena; written by peers with system-scope stores
     unsigned long long halo_epoch[2];              // [0] by the lower neighbour, [1] by the upper
@@ -99,7 +100,8 @@ struct NsbSlabDesc {                 // what a rank tells its peers (POD, travel
     long long pitch;
     long long off_u, off_v, off_G, off_rhs, off_p[2], off_sync, off_sorflag, off_gband;   // byte offsets in the arena
     long long arena_bytes;
-    unsigned long long reserved[4];
+    unsigned char uuid[16];          // cudaDeviceProp::uuid of the owner's GPU
+    unsigned long long reserved[2];
 };
 
 struct SlabPeer {                    // a peer as seen from this rank (device pointers valid HERE)
@@ -107,7 +109,7 @@ struct SlabPeer {                    // a peer as seen from this rank (device po
     double *u, *v, *G, *rhs, *p[2];
     SlabSync* sync;
     unsigned long long* sorflag;     // [2][n_strips]: [0] written by ITS lower neighbour, [1] by its upper
-    double* gband;                   // [2 parities][NSB_RED_Q][nbands_global]
+    double* gband;                   // [NSB_RED_DEPTH][NSB_RED_Q][nbands_global]
     int nj;
     bool mapped_ipc;
 };
@@ -145,6 +147,7 @@ struct nsb_ctx {
     NsbSlabDesc desc;
     SlabPeer peer[NSB_MAX_RANKS];      // peer[rank] is this rank itself
     bool connected;
+    bool peers_distinct;               // every rank of the decomposition sits on a different physical GPU
     SlabSync* d_sync; unsigned long long* d_sorflag; double* d_gband;
     unsigned long long seq;            // SOR iterations executed so far (halo flag values)
     unsigned long long red_round;      // collective reduction rounds completed so far

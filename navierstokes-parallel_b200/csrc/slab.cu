@@ -8,6 +8,7 @@
 // flag (slab.cuh).  NCCL / gloo (through torch.distributed in the python host, or any other channel
 // in a C host) only carries the 256-byte descriptors once, at start-up.
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <unistd.h>
 
@@ -182,6 +183,11 @@ extern "C" int nsb_slab_connect(nsb_ctx* c, const void* descs) {
         p.gband = (double*)(p.base + d.off_gband);
         p.nj = d.nj;
     }
+    c->peers_distinct = true;
+    for (int r = 0; r < c->world; r++)
+        for (int q = r + 1; q < c->world; q++)
+            if (memcmp(D[r].uuid, D[q].uuid, 16) == 0) c->peers_distinct = false;
+    if (getenv("NSB_SLAB_LOCKSTEP")) c->peers_distinct = false;    // force the one-launch-per-iteration sweep
     c->connected = true;
     return NSB_OK;
 }

@@ -63,10 +63,10 @@ __device__ __forceinline__ double warp_ordered_max(const double* v, int n, int l
 
 // ---- collective reduction, part 1 (any block, all threads): contribute this rank's band values.
 // vals[q * nb_local + b] for q < nq.  Writes them into every rank's gather buffer (parity
-// round & 1), then tells every rank that this rank has contributed to `round`.
+// round & 3), then tells every rank that this rank has contributed to `round`.
 __device__ __forceinline__ void slab_red_contribute(const SlabRed& sr, unsigned long long round, int nq,
                                                     const double* vals) {
-    const int par = (int)(round & 1ull);
+    const int par = (int)(round & (unsigned long long)(NSB_RED_DEPTH - 1));
     for (int r = 0; r < sr.world; r++) {
         double* dst = sr.gband[r] + (size_t)par * NSB_RED_Q * sr.nb_global;
         for (int x = threadIdx.x; x < nq * sr.nb_local; x += blockDim.x) {
@@ -88,7 +88,7 @@ __device__ __forceinline__ void slab_red_finish(const SlabRed& sr, unsigned long
     if ((int)threadIdx.x < sr.world)
         spin_until_ge(&sr.sync[sr.rank]->red_arrived[threadIdx.x], round + 1ull, &sr.sync[sr.rank]->error);
     __syncthreads();
-    const int par = (int)(round & 1ull);
+    const int par = (int)(round & (unsigned long long)(NSB_RED_DEPTH - 1));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp < nq) {
         const double* src = sr.gband[sr.rank] + ((size_t)par * NSB_RED_Q + warp) * sr.nb_global;
@@ -97,4 +97,35 @@ __device__ __forceinline__ void slab_red_finish(const SlabRed& sr, unsigned long
         if (lane == 0) out[warp] = v;
     }
     __syncthreads();
+}
+
+
+// ---- the same collective reduction driven by ONE WARP (persistent sweep: the warp that closes an
+// iteration).  Same buffers, same flags, same summation order as the block versions above.
+__device__ __forceinline__ void slab_red_contribute_warp(const SlabRed& sr, unsigned long long round, int nq,
+                                                         const double* vals, int lane) {
+    const int par = (int)(round & (unsigned long long)(NSB_RED_DEPTH - 1));
+    for (int r = 0; r < sr.world; r++) {
+        double* dst = sr.gband[r] + (size_t)par * NSB_RED_Q * sr.nb_global;
+        for (int x = lane; x < nq * sr.nb_local; x += 32) {
+            const int q = x / sr.nb_local, b = x - q * sr.nb_local;
+            dst[(size_t)q * sr.nb_global + sr.band0 + b] = __ldcg(vals + x);
+        }
+    }
+    __threadfence_system();
+    __syncwarp();
+    if (lane < sr.world) st_release_sys(&sr.sync[lane]->red_arrived[sr.rank], round + 1ull);
+}
+
+// Returns false if a rank did not arrive in time.  out = combined value of quantity 0 (a SUM).
+__device__ __forceinline__ bool slab_red_finish_sum_warp(const SlabRed& sr, unsigned long long round, int lane,
+                                                         double* out) {
+    int ok = 1;
+    if (lane < sr.world)
+        ok = spin_until_ge(&sr.sync[sr.rank]->red_arrived[lane], round + 1ull, &sr.sync[sr.rank]->error) ? 1 : 0;
+    ok = __all_sync(0xffffffffu, ok);
+    const int par = (int)(round & (unsigned long long)(NSB_RED_DEPTH - 1));
+    const double* src = sr.gband[sr.rank] + (size_t)par * NSB_RED_Q * sr.nb_global;
+    *out = warp_ordered_sum(src, sr.nb_global, lane);
+    return ok != 0;
 }

@@ -502,7 +502,7 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
         t.bar_base = smem_u32(smem_raw + SOR_WARPS * SOR_WARP_SMEM + warp * 2 * SOR_NST * 8);
 
         // ---- y-slab: the halo rows this task reads were stored by the neighbour's launch seq-1
-        if (a.world > 1) {
+        if (a.world > 1 && a.it > 0) {    // it == 0: the halo came with the p exchange at the solve entry
             const bool need_down = !t.wall_bottom && t.jc0 - 3 <= 0;
             const bool need_up = !t.wall_top && t.jc1 + 3 >= a.nj + 1;
             if (lane < 3) {
@@ -598,6 +598,11 @@ struct SorPersistArgs {
     unsigned long long* done;        // [n_tasks] epoch of the last iteration the task finished
     unsigned long long flag_base;    // epoch of "before iteration 0 of this launch"
     double* partials2;               // [2][n_tasks]
+    // y-slabs: this rank's two pressure buffers and the neighbours' (index = buffer number), the buffer
+    // iteration 0 reads, and the reduction round of iteration 0
+    double* own_p[2]; double* down_p[2]; double* up_p[2];
+    int buf0;
+    unsigned long long round0;
 };
 
 __device__ __forceinline__ unsigned long long ld_acquire_gpu(const unsigned long long* p) {
@@ -654,7 +659,10 @@ __global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
         const int it = (int)(id / (unsigned long long)a.n_tasks);
         const int task = (int)(id - (unsigned long long)it * (unsigned long long)a.n_tasks);
         const int strip = task % a.n_strips;
-        const int chunk = task / a.n_strips;
+        int chunk = task / a.n_strips;
+        if (a.world > 1 && a.n_chunks > 1)     // slab boundaries first: their rows travel while the interior is swept
+            chunk = (chunk == 0) ? 0 : (chunk == 1) ? a.n_chunks - 1 : chunk - 1;
+        const int tslot = chunk * a.n_strips + strip;      // index of this task's flag and partial
 
         // ---- may this iteration run?  iteration it-2 must be closed, and nothing before may have converged
         // (the wait also keeps the double-buffered partials and the 4 tickets of iteration it-2 / it-4 safe,
@@ -689,8 +697,9 @@ __global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
             asm volatile("fence.proxy.async;" ::: "memory");   // other warps' generic stores -> this warp's TMA reads
         }
 
-        const double* pin = (it & 1) ? a.pout : a.pin;
-        double* pout = (it & 1) ? const_cast<double*>(a.pin) : a.pout;
+        const int bo = (pa.buf0 + it + 1) & 1;              // buffer this iteration writes
+        const double* pin = pa.own_p[bo ^ 1];
+        double* pout = pa.own_p[bo];
 
         const int g0 = strip * NSB_STRIP_GROUPS;
         const int g = g0 + lane;
@@ -715,9 +724,11 @@ __global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
         t.jc1 = min(t.jc0 + a.chunk_rows - 1, a.nj);
         t.jstart = t.jc0 - 3;
         t.nj = a.nj;
-        t.wall_bottom = true; t.wall_top = true;
-        t.rlo = 1; t.rhi = a.nj;
-        t.push_down = false; t.push_up = false;
+        t.wall_bottom = a.wall_bottom != 0; t.wall_top = a.wall_top != 0;
+        t.rlo = t.wall_bottom ? 1 : -1;
+        t.rhi = t.wall_top ? a.nj : a.nj + 2;
+        t.push_down = !t.wall_bottom && t.jc0 <= 3;
+        t.push_up = !t.wall_top && t.jc1 >= a.nj - 2;
         t.pitch = a.pitch;
         t.lane = lane;
         t.zero = a.zero;
@@ -728,12 +739,32 @@ __global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
         t.j_next = t.jstart;
         t.j_limit = min(t.jc1 + 3, a.nj + 3);
         t.pout_row = pout + row_first - 2 * a.pitch + coff + (long long)lane * NSB_GROUP;
-        t.down_col = pout; t.up_col = pout; t.down_nj = 0;
+        t.down_col = pa.down_p[bo] + coff + (long long)lane * NSB_GROUP;
+        t.up_col = pa.up_p[bo] + coff + (long long)lane * NSB_GROUP;
+        t.down_nj = a.down_nj;
         const int groups_here = min(32, a.n_groups - g0);
         t.copy_bytes = (uint32_t)groups_here * 32u;
         t.lds_lane = reinterpret_cast<const double*>(ring) + lane * NSB_GROUP;
         t.smem_base = smem_u32(ring);
         t.bar_base = bar_base;
+
+        // ---- y-slab: rows of the previous iteration pushed by the neighbouring ranks (their boundary
+        //      tasks of iteration it-1, strips s-1 .. s+1); a.seq = halo epoch of "before iteration 0"
+        if (a.world > 1 && it > 0) {
+            const bool need_down = !t.wall_bottom && t.jc0 - 3 <= 0;
+            const bool need_up = !t.wall_top && t.jc1 + 3 >= a.nj + 1;
+            int ok2 = 1;
+            if (lane < 3) {
+                const int sidx = strip - 1 + lane;
+                if (sidx >= 0 && sidx < a.n_strips) {
+                    if (need_down) ok2 = spin_until_ge(a.flag_from_down + sidx, a.seq + (unsigned long long)it, a.err) ? 1 : 0;
+                    if (need_up && ok2) ok2 = spin_until_ge(a.flag_from_up + sidx, a.seq + (unsigned long long)it, a.err) ? 1 : 0;
+                }
+            }
+            ok2 = __all_sync(FULLM, ok2);
+            if (!ok2) break;
+            asm volatile("fence.proxy.async;" ::: "memory");
+        }
 
         t.full_par = full_par; t.empty_par = empty_par;
         {
@@ -751,14 +782,22 @@ __global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
         else acc = sor_run_task<RECIP, false>(t, a.k, lg);
         acc = warp_sum(acc);
         double* part = pa.partials2 + (size_t)(it & 1) * a.n_tasks;
-        if (lane == 0) part[task] = acc;
+        if (lane == 0) part[tslot] = acc;
 
         // ---- publish: rows and partial are out
         __threadfence();
         __syncwarp();
         unsigned long long tk = 0;
+        if (t.push_down || t.push_up) {                      // halo rows are out: tell the neighbouring rank(s)
+            __threadfence_system();
+            __syncwarp();
+            if (lane == 0) {
+                if (t.push_down) st_release_sys(a.down_flag + strip, a.seq + (unsigned long long)it + 1ull);
+                if (t.push_up) st_release_sys(a.up_flag + strip, a.seq + (unsigned long long)it + 1ull);
+            }
+        }
         if (lane == 0) {
-            st_release_gpu(pa.done + task, pa.flag_base + (unsigned long long)it + 1ull);
+            st_release_gpu(pa.done + tslot, pa.flag_base + (unsigned long long)it + 1ull);
             tk = atomicAdd(pa.claim + 1 + (it & 3), 1ull);
         }
         tk = __shfl_sync(FULLM, tk, 0);
@@ -772,23 +811,41 @@ __global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
             }
             __threadfence();
             __syncwarp();
-            const double tot = warp_ordered_sum(a.bandvals, a.n_chunks, lane);
+            // iterations close in order; nothing closes (and no reduction round is spent) after the one
+            // that converged -- every rank sees the same residual bits, so every rank decides the same
+            int skip = 0;
             if (lane == 0) {
-                // iterations close in order; nothing closes after the one that converged
                 const unsigned long long t0 = global_timer_ns();
                 while (ld_acquire_gpu_s32(&a.ctl->iters) < a.it + it) {
-                    if (global_timer_ns() - t0 > NSB_SPIN_TIMEOUT_NS) { *((volatile int*)a.err) = 1; break; }
+                    if (a.check && ld_acquire_gpu_s32(&a.ctl->converged)) break;
+                    if (global_timer_ns() - t0 > NSB_SPIN_TIMEOUT_NS) { *((volatile int*)a.err) = 1; skip = 1; break; }
                     __nanosleep(64);
                 }
-                if (!(a.check && ld_acquire_gpu_s32(&a.ctl->converged))) sor_close_iteration(tot, a.ctl, a.it + it, a.k.cells);
+                if (a.check && ld_acquire_gpu_s32(&a.ctl->converged)) skip = 1;
+            }
+            skip = __shfl_sync(FULLM, skip, 0);
+            if (!skip) {
+                double tot;
+                if (a.world > 1) {
+                    const unsigned long long round = pa.round0 + (unsigned long long)it;
+                    slab_red_contribute_warp(a.red, round, 1, a.bandvals, lane);
+                    slab_red_finish_sum_warp(a.red, round, lane, &tot);
+                } else {
+                    tot = warp_ordered_sum(a.bandvals, a.n_chunks, lane);
+                }
+                if (lane == 0) sor_close_iteration(tot, a.ctl, a.it + it, a.k.cells);
             }
             __syncwarp();
         }
     }
 }
 
+// y-slabs: only when every rank sits on a GPU of its own -- the kernels of neighbouring ranks wait
+// for each other, so they must be able to run at the same time (a 1-GPU box emulates the ranks with
+// the one-launch-per-iteration kernel in lock step instead).
 int nsb_sor_persist_supported(const nsb_ctx* c) {
-    return c->world == 1 && c->chunk_rows >= 4;
+    if (c->chunk_rows < 4) return 0;
+    return c->world == 1 || (c->connected && c->peers_distinct);
 }
 
 // world > 1: the closing of an iteration is its own one-block kernel, so that the sweep kernel never
@@ -922,8 +979,30 @@ cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int n_iter, int check) {
     a.k.inv_cells_unused = 0.0;
     a.k.cells = (long long)c->g.ni * (long long)c->J;
     a.partials = c->d_partials; a.bandvals = c->d_bandvals; a.ctl = c->d_ctl;
-    a.world = 1; a.wall_bottom = 1; a.wall_top = 1;
+    a.world = c->world; a.wall_bottom = c->wall_bottom; a.wall_top = c->wall_top;
     a.err = &c->d_sync->error;
+    a.seq = c->seq;
+    a.red = nsb_slab_red(c);
+    pa.round0 = c->red_round;
+    pa.buf0 = c->pcur;
+    for (int k = 0; k < 2; k++) { pa.own_p[k] = c->pbuf[k]; pa.down_p[k] = c->pbuf[k]; pa.up_p[k] = c->pbuf[k]; }
+    a.down_nj = 0;
+    a.flag_from_down = c->d_sorflag; a.flag_from_up = c->d_sorflag + c->n_strips;
+    a.down_flag = c->d_sorflag; a.up_flag = c->d_sorflag;
+    if (c->world > 1) {
+        if (!c->connected) return cudaErrorNotReady;
+        if (!c->wall_bottom) {
+            const SlabPeer& d = c->peer[c->rank - 1];
+            pa.down_p[0] = d.p[0]; pa.down_p[1] = d.p[1]; a.down_nj = d.nj;
+            a.down_flag = d.sorflag + c->n_strips;             // I am its UPPER neighbour
+        }
+        if (!c->wall_top) {
+            const SlabPeer& u = c->peer[c->rank + 1];
+            pa.up_p[0] = u.p[0]; pa.up_p[1] = u.p[1];
+            a.up_flag = u.sorflag;                             // I am its LOWER neighbour
+        }
+    }
+    c->seq += (unsigned long long)n_iter + 1ull;               // halo epochs: iterations ATTEMPTED, like flag_base
     pa.n_iter = n_iter;
     pa.claim = c->d_claim; pa.done = c->d_done; pa.partials2 = c->d_partials2;
     pa.flag_base = c->flag_base;

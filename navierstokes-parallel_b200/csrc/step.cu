@@ -151,7 +151,10 @@ static int pick_engine(const nsb_ctx* c) {
         const char* env = getenv("NSB_SOR_ENGINE");
         if (env) e = atoi(env);
     }
-    if (c->world > 1) return NSB_SOR_STREAM_LAUNCH;            // the only slab-aware engine
+    if (c->world > 1) {                                        // slab-aware engines: the two streaming ones
+        if (e == NSB_SOR_STREAM_LAUNCH || !nsb_sor_persist_supported(c)) return NSB_SOR_STREAM_LAUNCH;
+        return NSB_SOR_STREAM;
+    }
     if (e == NSB_SOR_AUTO) e = nsb_sor_resident_supported(c) ? NSB_SOR_RESIDENT : NSB_SOR_STREAM;
     if (e == NSB_SOR_RESIDENT && !nsb_sor_resident_supported(c)) e = NSB_SOR_STREAM;
     if (e == NSB_SOR_STREAM && !nsb_sor_persist_supported(c)) e = NSB_SOR_STREAM_LAUNCH;
@@ -177,9 +180,12 @@ static int sor_iterate(nsb_ctx** cs, int n, int max_it, int check) {
         CU(c0, nsb_launch_sor_resident(c0, max_it, check));
         return NSB_OK;
     }
-    if (engine == NSB_SOR_STREAM) {                            // single slab: every iteration in one launch
-        CU(c0, cudaSetDevice(c0->device));
-        CU(c0, nsb_launch_sor_persist(c0, max_it, check));
+    if (engine == NSB_SOR_STREAM) {                            // every iteration of the solve in one launch per rank
+        for (int r = 0; r < n; r++) {
+            nsb_ctx* c = cs[r];
+            CU(c, cudaSetDevice(c->device));
+            CU(c, nsb_launch_sor_persist(c, max_it, check));
+        }
         return NSB_OK;
     }
     const int depth = c0->O.sor_check_batch > 0 ? c0->O.sor_check_batch : 24;
@@ -232,7 +238,7 @@ int nsb_ph_sor_end(nsb_ctx* c, int unused) {
         if (iters > 0 && c->last_sor_engine == NSB_SOR_STREAM_LAUNCH)
             CU(c, nsb_launch_sor_finish_ghosts(c, c->pbuf[c->pcur], c->pbuf[c->pcur ^ 1]));
     }
-    c->seq += (unsigned long long)iters;
+    if (c->last_sor_engine != NSB_SOR_STREAM) c->seq += (unsigned long long)iters;   // (the persistent launch advanced it)
     c->red_round += (unsigned long long)iters;
     CU(c, cudaEventRecord(c->ev1, c->stream));
     CU(c, cudaEventSynchronize(c->ev1));

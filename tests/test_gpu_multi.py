@@ -1,0 +1,62 @@
+"""y-slab decomposition on SEVERAL GPUs (needs >= 2 devices; skipped on a 1-GPU box): every slab on a
+device of its own, halo rows and reduction bands travelling as peer stores over NVLink inside the
+persistent sweep kernels.  The bar is the same as on one GPU: the bits of the undivided run."""
+import numpy as np
+import pytest
+
+from util import nsb
+
+pytestmark = pytest.mark.gpu
+
+
+def _ndev():
+    import torch
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+def _rand(shape, seed):
+    return np.ascontiguousarray(np.random.default_rng(seed).uniform(-1, 1, shape))
+
+
+def _worlds():
+    return [w for w in (2, 4, 8) if w <= max(_ndev(), 0)] or [2]
+
+
+@pytest.mark.parametrize("world", _worlds())
+@pytest.mark.parametrize("ni,nj,chunk", [(300, 256, 16), (1000, 960, 120)])
+def test_sor_iterations_equal_single_slab_multi_gpu(world, ni, nj, chunk):
+    if _ndev() < world:
+        pytest.skip(f"needs {world} GPUs")
+    m = nsb()
+    if (nj + chunk - 1) // chunk < world:
+        pytest.skip("fewer bands than slabs")
+    P = m.make_params(i_max=ni, j_max=nj, a=1.0, b=1.0, T=1.0, max_it=300)
+    p0, r0 = _rand((ni + 2, nj + 2), 5), _rand((ni + 2, nj + 2), 6)
+    with m.Solver(P, sor_engine=m.SOR_STREAM, chunk_rows=chunk) as s:
+        s.upload(m.P, p0); s.upload(m.RHS, r0)
+        res1 = [s.sor_iterations(1), s.sor_iterations(2), s.sor_iterations(25)]
+        want = s.download(m.P)
+    with m.Group(P, list(range(world)), chunk_rows=chunk) as g:
+        g.upload(m.P, p0); g.upload(m.RHS, r0)
+        resg = [g.sor_iterations(1), g.sor_iterations(2), g.sor_iterations(25)]
+        got = g.download(m.P)
+    assert np.array_equal(got[1:-1, 1:-1], want[1:-1, 1:-1])
+    assert resg == res1
+
+
+@pytest.mark.parametrize("world", _worlds())
+def test_whole_run_equals_single_slab_multi_gpu(world):
+    if _ndev() < world:
+        pytest.skip(f"needs {world} GPUs")
+    m = nsb()
+    P = m.make_params(i_max=200, j_max=192, a=1.0, b=1.0, T=1.0, Re=1000.0, max_it=400, epsilon=1e-4)
+    with m.Solver(P, sor_engine=m.SOR_STREAM, chunk_rows=16) as s:
+        log1, _ = s.run(max_steps=5)
+        f1 = [s.download(f) for f in (m.U, m.V, m.P)]
+    with m.Group(P, list(range(world)), chunk_rows=16) as g:
+        logg, _ = g.run(max_steps=5)
+        fg = [g.download(f) for f in (m.U, m.V, m.P)]
+    for k in ("sor_iters", "dt", "res", "norm_p", "u_max", "v_max"):
+        assert [x[k] for x in logg] == [x[k] for x in log1], k
+    for a, b in zip(fg, f1):
+        assert np.array_equal(a[1:-1, 1:-1], b[1:-1, 1:-1])
