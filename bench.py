@@ -219,7 +219,9 @@ def main():
         nj_local = nj
     else:
         # one slab per process; NCCL only carries the 256-byte slab descriptors, once
-        s = m.SlabSolver(P, rank, world, m.torch_all_gather(), device=local, chunk_rows=args.chunk_rows)
+        # 128-row bands deal 8192 rows per GPU out evenly (120-row bands would leave one rank a band more)
+        ch = args.chunk_rows or (128 if (nj // world) % 128 == 0 else 0)
+        s = m.SlabSolver(P, rank, world, m.torch_all_gather(), device=local, chunk_rows=ch)
         nj_local = s.nj
     cells_local = float(ni) * float(nj_local)
     stream = torch.cuda.ExternalStream(s.stream, device=torch.device("cuda", local))
@@ -268,7 +270,7 @@ def main():
     achieved = 24.0 * cells_local / (k_ms * 1e-3) / 1e9
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "sor_stream_traffic.json"))).get("dram_bytes_per_launch")
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "sor_stream_traffic.json"))).get("dram_bytes_per_iteration") * n_k
     except Exception:
         pass
     roofline = {"bound": "hbm", "kernel": "sor_persist_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
