@@ -98,14 +98,14 @@ def test_layout_roundtrip_both_layouts():
 SOR_SHAPES = [(8, 8), (16, 16), (31, 17), (120, 40), (121, 33), (257, 64), (64, 300), (500, 7), (3, 3), (1, 9), (9, 1)]
 
 
-@pytest.mark.parametrize("engine", ["stream", "launch", "simple"])
+@pytest.mark.parametrize("engine", ["stream", "launch", "simple", "resident"])
 @pytest.mark.parametrize("ni,nj", SOR_SHAPES)
 def test_sor_per_iteration_bit_exact(engine, ni, nj):
     """p after 1, 2, 3, +5 iterations equals the oracle's red-black iterate bit for bit, residual
     norm to 1e-12 relative; sizes include non-multiples of every tile dimension (the reference's
     CUDA kernel is wrong for those)."""
     m = nsb()
-    eng = dict(stream=m.SOR_STREAM, launch=m.SOR_STREAM_LAUNCH, simple=m.SOR_SIMPLE)[engine]
+    eng = dict(stream=m.SOR_STREAM, launch=m.SOR_STREAM_LAUNCH, simple=m.SOR_SIMPLE, resident=m.SOR_RESIDENT)[engine]
     a, b = 1.0, 0.9
     s, P = _solver(m, engine=eng, i_max=ni, j_max=nj, a=a, b=b, omega=1.7)
     L = ob.lib()
@@ -147,12 +147,12 @@ def test_sor_division_modes(div_mode):
     s.close()
 
 
-@pytest.mark.parametrize("engine", ["stream", "launch", "simple"])
+@pytest.mark.parametrize("engine", ["stream", "launch", "simple", "resident"])
 def test_sor_convergence_iteration_count(engine):
     """Converged solve: same iteration count, same return value (it+1), bit-equal p; then the
     not-converged contract (-1, p = last iterate)."""
     m = nsb()
-    eng = dict(stream=m.SOR_STREAM, launch=m.SOR_STREAM_LAUNCH, simple=m.SOR_SIMPLE)[engine]
+    eng = dict(stream=m.SOR_STREAM, launch=m.SOR_STREAM_LAUNCH, simple=m.SOR_SIMPLE, resident=m.SOR_RESIDENT)[engine]
     ni, nj = 48, 40
     s, P = _solver(m, engine=eng, i_max=ni, j_max=nj, epsilon=1e-5, max_it=5000)
     p = np.zeros(s.shape)
@@ -201,10 +201,10 @@ def _compare_run(m, c, engine):
     s.close()
 
 
-@pytest.mark.parametrize("engine", ["stream", "launch", "simple"])
+@pytest.mark.parametrize("engine", ["stream", "launch", "simple", "resident"])
 def test_whole_run_matches_committed_redblack_fixtures(engine):
     m = nsb()
-    eng = dict(stream=m.SOR_STREAM, launch=m.SOR_STREAM_LAUNCH, simple=m.SOR_SIMPLE)[engine]
+    eng = dict(stream=m.SOR_STREAM, launch=m.SOR_STREAM_LAUNCH, simple=m.SOR_SIMPLE, resident=m.SOR_RESIDENT)[engine]
     cases = [c for c in json.load(open(os.path.join(GOLD, "runs.json"))) if c["sor_order"] == 1]
     assert len(cases) >= 4
     for c in cases:
