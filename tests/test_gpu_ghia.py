@@ -7,6 +7,8 @@ its Re=10000 rows and is not used).  The scheme is first-order donor-cell at the
 computes (main.c:92), so agreement is a BAND that tightens with resolution -- the serial reference itself
 is off by 0.015 (u) / 0.027 (v) at 64^2, Re=100.  Exact agreement of the GPU path with the
 reference algorithm is the business of test_gpu_parity.py; here the converged flow is checked."""
+import os
+
 import numpy as np
 import pytest
 
@@ -42,9 +44,17 @@ def centerlines(m, s, n):
     return np.interp(Y[::-1], yy, ucl)[::-1], np.interp(X[::-1], xx, vcl)[::-1]
 
 
-@pytest.mark.parametrize("Re,n,T,tol_u,tol_v", [(100, 64, 20.0, 0.03, 0.04), (100, 128, 20.0, 0.02, 0.025),
-                                                (1000, 128, 60.0, 0.10, 0.12), (1000, 256, 60.0, 0.06, 0.08)])
-def test_centerlines_match_ghia(Re, n, T, tol_u, tol_v):
+# measured on B200 (profiles/r1e_ghia.txt): Re=100: 64^2 0.0023 / 0.0074, 128^2 0.0043 / 0.0087;
+# Re=1000: 128^2 0.0436 / 0.0436, 256^2 0.0193 / 0.0192 (max |u - Ghia| / max |v - Ghia|).
+# The two larger runs take ~1 min each on the GPU and only run with NSB_SLOW_TESTS=1.
+CASES = [(100, 64, 20.0, 0.01, 0.015, False), (1000, 128, 60.0, 0.06, 0.06, False),
+         (100, 128, 20.0, 0.01, 0.015, True), (1000, 256, 60.0, 0.03, 0.03, True)]
+
+
+@pytest.mark.parametrize("Re,n,T,tol_u,tol_v,slow", CASES)
+def test_centerlines_match_ghia(Re, n, T, tol_u, tol_v, slow):
+    if slow and not os.environ.get("NSB_SLOW_TESTS"):
+        pytest.skip("long run: set NSB_SLOW_TESTS=1")
     m = nsb()
     P = m.make_params(i_max=n, j_max=n, a=1.0, b=1.0, T=T, Re=float(Re), tau=0.5, omega=1.7, epsilon=1e-5, max_it=1000)
     with m.Solver(P) as s:                                    # NSB_SOR_AUTO: the cluster-resident engine at these sizes
