@@ -18,6 +18,7 @@
 // block (fixed tree) and over the CTAs in rank order: deterministic, but not the summation order of
 // the streaming engine -- only the convergence test sees it.
 #include <cooperative_groups.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "nsb_internal.h"
@@ -41,55 +42,85 @@ struct ResidentArgs {
     SorCtl* ctl;
 };
 
-// One colour pass over the rows 1..R of this CTA's tile.  Thread layout: tx along column PAIRS
-// (columns 2q+1, 2q+2), ty along rows.  WITH_RES: also accumulate r^2 of the cells just updated
-// (valid for the second colour: all their neighbours are final).
-template <bool RECIP, bool UPDATE>
-__device__ __forceinline__ double resident_pass(double* __restrict__ P, const double* __restrict__ Q, int W, int R,
-                                                int ni, int jlo, int color, bool with_res, const SorCoef& kf,
-                                                int tx, int ty, int TX, int TY) {
+// Final ghost values as the reference leaves them (the refresh before the LAST black sweep,
+// main.cu:694): kept beside the working ghost cells, which follow every update at once.
+struct GhostFinal {
+    double* w; double* e;      // [rows_per_cta + 2] per tile row l
+    double* s; double* n;      // [W] per x index (first / last CTA only)
+};
+
+// MODE 0: update the cells of `color` (backup of the old value into B when B != nullptr);
+//         with_res: also accumulate r^2 of the cells just updated (second colour: neighbours final).
+// MODE 1: residual only.   MODE 2: roll the cells of `color` back from B.
+// Thread layout: tx along column PAIRS (columns 2q+1, 2q+2), ty along rows.
+// Ghost cells are owned by the thread of the wall-adjacent cell: it refreshes them right after its
+// update, which is what the reference's refresh before the next colour would copy; the black
+// cell's residual is taken BEFORE its ghost follows, so it sees the pre-black value (main.cu:694-702).
+template <bool RECIP, int MODE>
+__device__ __forceinline__ double resident_pass(double* __restrict__ P, const double* __restrict__ Q, double* __restrict__ B,
+                                                const GhostFinal& gf, int W, int R, int ni, int nj, int jlo, int color,
+                                                bool with_res, const SorCoef& kf, int tx, int ty, int TX, int TY) {
     double acc = 0.0;
     const int npairs = (ni + 1) >> 1;
-    for (int l = 1 + ty; l <= R; l += TY) {
-        const int j = jlo + l - 1;                                  // global row
-        double* row = P + (size_t)l * W;
-        const double* rq = Q + (size_t)(l - 1) * W;
-        for (int q = tx; q < npairs; q += TX) {
-            // the cell of this pair with (i + j) % 2 == color
-            const int i = 2 * q + 1 + ((j + 1 + color) & 1);        // i = 2q+1 if (2q+1+j)%2 == color else 2q+2
+    // the cells of one pass are independent of each other: the row loop is unrolled so that the loads and
+    // the FP64 chains of several cells overlap (the pass is latency-bound: a handful of cells per thread)
+    for (int q = tx; q < npairs; q += TX)
+#pragma unroll 4
+        for (int l = 1 + ty; l <= R; l += TY) {
+            const int j = jlo + l - 1;                              // global row
+            double* row = P + (size_t)l * W;
+            const double* rq = Q + (size_t)(l - 1) * W;
+            const int i = 2 * q + 1 + ((j + 1 + color) & 1);        // the cell of this pair with (i + j) % 2 == color
             if (i > ni) continue;
             const int x = i + 1;
+            if (MODE == 2) {
+                const double v = B[(size_t)l * W + x];
+                row[x] = v;
+                if (i == 1) { row[1] = v; gf.w[l] = v; }
+                if (i == ni) { row[ni + 2] = v; gf.e[l] = v; }
+                if (j == 1) { row[x - W] = v; gf.s[x] = v; }
+                if (j == nj) { row[x + W] = v; gf.n[x] = v; }
+                continue;
+            }
             const double pc = row[x], pe = row[x + 1], pw = row[x - 1];
             const double pn = row[x + W], ps = row[x - W];
             const double r = rq[x];
-            if (UPDATE) {
+            if (MODE == 0) {
                 const double v = sor_cell<RECIP>(pc, pe, pw, pn, ps, r, kf);
+                if (B) B[(size_t)l * W + x] = pc;
                 row[x] = v;
                 if (with_res) {
                     const double d = sor_residual<RECIP>(v, pe, pw, pn, ps, r, kf);
                     acc = fma(d, d, acc);
                 }
+                // ghosts follow; the value the reference's LAST refresh would have copied is the new one for
+                // the first colour and the old one for the second
+                const double fin = (color == 0) ? v : pc;
+                if (i == 1) { row[1] = v; gf.w[l] = fin; }
+                if (i == ni) { row[ni + 2] = v; gf.e[l] = fin; }
+                if (j == 1) { row[x - W] = v; gf.s[x] = fin; }
+                if (j == nj) { row[x + W] = v; gf.n[x] = fin; }
             } else {
                 const double d = sor_residual<RECIP>(pc, pe, pw, pn, ps, r, kf);
                 acc = fma(d, d, acc);
             }
         }
-    }
     return acc;
 }
 
-// Neumann ghosts of this CTA's tile (main.cu:249-273): west / east columns for its rows, the bottom
-// ghost row on the first CTA, the top ghost row on the last.
-__device__ __forceinline__ void resident_ghosts(double* P, int W, int R, int ni, bool first, bool last) {
+// Neumann ghosts of this CTA's tile (main.cu:249-273), once at the start of the solve.
+__device__ __forceinline__ void resident_ghosts(double* P, const GhostFinal& gf, int W, int R, int ni, bool first, bool last) {
     for (int l = 1 + (int)threadIdx.x; l <= R; l += RES_THREADS) {
         double* row = P + (size_t)l * W;
-        row[1] = row[2];                    // p[0][j] = p[1][j]
-        row[ni + 2] = row[ni + 1];          // p[i_max+1][j] = p[i_max][j]
+        row[1] = row[2]; gf.w[l] = row[2];                          // p[0][j] = p[1][j]
+        row[ni + 2] = row[ni + 1]; gf.e[l] = row[ni + 1];           // p[i_max+1][j] = p[i_max][j]
     }
     if (first)
-        for (int i = 1 + (int)threadIdx.x; i <= ni; i += RES_THREADS) P[i + 1] = P[W + i + 1];                    // p[i][0] = p[i][1]
+        for (int i = 1 + (int)threadIdx.x; i <= ni; i += RES_THREADS) { P[i + 1] = P[W + i + 1]; gf.s[i + 1] = P[W + i + 1]; }
     if (last)
-        for (int i = 1 + (int)threadIdx.x; i <= ni; i += RES_THREADS) P[(size_t)(R + 1) * W + i + 1] = P[(size_t)R * W + i + 1];
+        for (int i = 1 + (int)threadIdx.x; i <= ni; i += RES_THREADS) {
+            P[(size_t)(R + 1) * W + i + 1] = P[(size_t)R * W + i + 1]; gf.n[i + 1] = P[(size_t)R * W + i + 1];
+        }
 }
 
 template <bool RECIP>
@@ -97,20 +128,23 @@ __global__ void __launch_bounds__(RES_THREADS, 1) sor_resident_kernel(const Resi
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ double red_sh[32];
     __shared__ double parts[RES_MAX_CLUSTER];
-    __shared__ int stop_flag;
     cg::cluster_group cluster = cg::this_cluster();
     const int C = (int)cluster.num_blocks();
     const int rank = (int)cluster.block_rank();
-    const int W = a.W, ni = a.ni;
+    const int W = a.W, ni = a.ni, nj = a.nj;
     const int jlo = 1 + rank * a.rows_per_cta;                         // first global row of this CTA
-    int R = min(a.rows_per_cta, a.nj - jlo + 1);
-    if (R < 0) R = 0;
-    const bool first = (rank == 0), last = (jlo + R - 1 == a.nj) && R > 0;
-    double* P = reinterpret_cast<double*>(smem_raw);                  // (rows_per_cta + 2) x W : rows jlo-1 .. jlo+R
-    double* Q = P + (size_t)(a.rows_per_cta + 2) * W;                 // rows_per_cta x W        : RHS of rows jlo .. jlo+R-1
+    const int R = min(a.rows_per_cta, nj - jlo + 1);                   // >= 1 by construction (resident_plan)
+    const bool first = (rank == 0), last = (jlo + R - 1 == nj);
+    const size_t tile = (size_t)(a.rows_per_cta + 2) * W;
+    double* P = reinterpret_cast<double*>(smem_raw);                  // rows jlo-1 .. jlo+R, x index = i + 1
+    double* B = P + tile;                                             // old values of the first colour (roll-back)
+    double* Q = B + tile;                                             // RHS rows jlo .. jlo+R-1
+    GhostFinal gf;
+    gf.w = Q + (size_t)a.rows_per_cta * W; gf.e = gf.w + (a.rows_per_cta + 2);
+    gf.s = gf.e + (a.rows_per_cta + 2); gf.n = gf.s + W;
     const int tid = threadIdx.x;
 
-    // ---- load the tile (row l of P = global row jlo - 1 + l), x index = i + 1
+    // ---- load the tile
     const double* gp = a.p + (long long)NSB_ROW0 * a.pitch + NSB_COL0;
     const double* gq = a.rhs + (long long)NSB_ROW0 * a.pitch + NSB_COL0;
     for (int l = 0; l <= R + 1; l++) {
@@ -126,74 +160,78 @@ __global__ void __launch_bounds__(RES_THREADS, 1) sor_resident_kernel(const Resi
     double* Pdown = (rank > 0) ? cluster.map_shared_rank(P, rank - 1) : nullptr;
     double* Pup = (rank + 1 < C) ? cluster.map_shared_rank(P, rank + 1) : nullptr;
     const int R_down = a.rows_per_cta;                                // every CTA below the last one is full
-    const bool has_up = (rank + 1 < C) && (jlo + R <= a.nj);          // rows exist above this CTA
-    const bool has_down = (rank > 0) && R > 0;
-    // thread layout for the passes
+    const bool has_up = (rank + 1 < C) && (jlo + R <= nj);
+    const bool has_down = (rank > 0);
     const int npairs = (ni + 1) >> 1;
     int TX = 32;
     while (TX < npairs && TX < RES_THREADS) TX <<= 1;
     const int TY = RES_THREADS / TX;
     const int tx = tid % TX, ty = tid / TX;
     const double thresh = a.ctl->thresh;
-    if (tid == 0) stop_flag = 0;
+    __syncthreads();
+    resident_ghosts(P, gf, W, R, ni, first, last);                                       // main.cu:686 of iteration 0
     __syncthreads();
     cluster.sync();
 
+    // Per iteration two cluster barriers.  The partial sums of iteration n become visible at the first
+    // barrier of iteration n+1, i.e. after its first colour has already run: that colour keeps the old
+    // values in B and is rolled back if iteration n turns out to have converged.
     int it = 0, converged = 0;
     double res = a.ctl->res, total = a.ctl->sum_r2;
-    for (; it < a.max_it; it++) {
-        double acc = 0.0;
-        for (int color = 0; color < 2; color++) {
-            if (R > 0) resident_ghosts(P, W, R, ni, first, last);                       // main.cu:686 / :694
+    for (;; it++) {
+        const bool real = it < a.max_it;
+        if (real) {
+            resident_pass<RECIP, 0>(P, Q, B, gf, W, R, ni, nj, jlo, 0, false, a.k, tx, ty, TX, TY);
             __syncthreads();
-            if (R > 0) acc += resident_pass<RECIP, true>(P, Q, W, R, ni, jlo, color, color == 1, a.k, tx, ty, TX, TY);
-            __syncthreads();
-            // boundary rows to the neighbours' halo rows: only the cells of this colour changed
-            if (has_down) {
-                const int j = jlo;                                                      // my row l = 1 -> their row R_down + 1
-                for (int i = 1 + ((j + 1 + color) & 1) + 2 * tid; i <= ni; i += 2 * RES_THREADS)
+            if (has_down)                                               // my row l = 1 -> their row R_down + 1 (cells of colour 0)
+                for (int i = 1 + ((jlo + 1) & 1) + 2 * tid; i <= ni; i += 2 * RES_THREADS)
                     Pdown[(size_t)(R_down + 1) * W + i + 1] = P[(size_t)W + i + 1];
-            }
-            if (has_up) {
-                const int j = jlo + R - 1;                                              // my row l = R -> their row 0
-                for (int i = 1 + ((j + 1 + color) & 1) + 2 * tid; i <= ni; i += 2 * RES_THREADS)
+            if (has_up)                                                 // my row l = R -> their row 0
+                for (int i = 1 + ((jlo + R) & 1) + 2 * tid; i <= ni; i += 2 * RES_THREADS)
                     Pup[i + 1] = P[(size_t)R * W + i + 1];
-            }
-            cluster.sync();
-        }
-        // residual of the red cells (their black neighbours are final now), ghosts as refreshed before colour 1
-        if (R > 0) acc += resident_pass<RECIP, false>(P, Q, W, R, ni, jlo, 0, false, a.k, tx, ty, TX, TY);
-        const double bsum = block_sum(acc, red_sh);
-        if (tid == 0) {
-            for (int r = 0; r < C; r++) {
-                double* dst = cluster.map_shared_rank(parts, r);
-                dst[rank] = bsum;
-            }
         }
         cluster.sync();
-        if (tid == 0) {
+        if (it > 0) {                                                   // close iteration it-1 (every thread, same order)
             double t = 0.0;
             for (int r = 0; r < C; r++) t += parts[r];
             total = t;
-            res = sqrt(t / (double)a.k.cells);                                          // main.cu:588
-            stop_flag = (res <= thresh) ? 1 : 0;                                        // main.cu:713
+            res = sqrt(t / (double)a.k.cells);                          // main.cu:588
+            converged = (res <= thresh) ? 1 : 0;                        // main.cu:713
         }
+        if (!real) break;
+        if (it > 0 && converged && a.check) {
+            resident_pass<RECIP, 2>(P, Q, B, gf, W, R, ni, nj, jlo, 0, false, a.k, tx, ty, TX, TY);
+            __syncthreads();
+            break;
+        }
+        double acc = resident_pass<RECIP, 0>(P, Q, nullptr, gf, W, R, ni, nj, jlo, 1, true, a.k, tx, ty, TX, TY);
         __syncthreads();
-        converged = stop_flag;
-        // `parts` is rewritten only after the next iteration's cluster barriers: no race with the reads above
-        if (converged && a.check) { it++; break; }
+        if (has_down)
+            for (int i = 1 + ((jlo + 2) & 1) + 2 * tid; i <= ni; i += 2 * RES_THREADS)
+                Pdown[(size_t)(R_down + 1) * W + i + 1] = P[(size_t)W + i + 1];
+        if (has_up)
+            for (int i = 1 + ((jlo + R + 1) & 1) + 2 * tid; i <= ni; i += 2 * RES_THREADS)
+                Pup[i + 1] = P[(size_t)R * W + i + 1];
+        cluster.sync();
+        // residual of the cells of colour 0: their neighbours are final now; ghosts next to them hold their own value
+        acc += resident_pass<RECIP, 1>(P, Q, nullptr, gf, W, R, ni, nj, jlo, 0, false, a.k, tx, ty, TX, TY);
+        const double bsum = block_sum(acc, red_sh);
+        if (tid == 0)
+            for (int r = 0; r < C; r++) cluster.map_shared_rank(parts, r)[rank] = bsum;
+        // (visible to every CTA after the next cluster barrier; rewritten only two barriers later)
     }
+    // `it` iterations are complete and closed
 
-    // ---- write the tile back: interior rows with their ghost columns, ghost rows on the first / last CTA
+    // ---- write the tile back: interior rows, ghost columns / rows as the reference leaves them
     double* gpw = a.p + (long long)NSB_ROW0 * a.pitch + NSB_COL0;
-    const int l0 = first ? 0 : 1, l1 = last ? R + 1 : R;
-    for (int l = l0; l <= l1 && R > 0; l++) {
+    for (int l = 1; l <= R; l++) {
         const long long ro = (long long)(jlo - 1 + l) * a.pitch;
-        const bool ghost_row = (l == 0) || (l == R + 1);
-        for (int i = tid; i <= ni + 1; i += RES_THREADS) {
-            if (ghost_row && (i == 0 || i == ni + 1)) continue;                         // corners: never written by the reference's reads
-            gpw[ro + i] = P[(size_t)l * W + i + 1];
-        }
+        for (int i = 1 + tid; i <= ni; i += RES_THREADS) gpw[ro + i] = P[(size_t)l * W + i + 1];
+        if (tid == 0 && it > 0) { gpw[ro] = gf.w[l]; gpw[ro + ni + 1] = gf.e[l]; }
+    }
+    if (it > 0) {
+        if (first) for (int i = 1 + tid; i <= ni; i += RES_THREADS) gpw[i] = gf.s[i + 1];
+        if (last) for (int i = 1 + tid; i <= ni; i += RES_THREADS) gpw[(long long)(nj + 1) * a.pitch + i] = gf.n[i + 1];
     }
     if (rank == 0 && tid == 0) {
         SorCtl* ctl = a.ctl;
@@ -214,9 +252,12 @@ static int resident_plan(const nsb_ctx* c, int* cluster, int* rows_per_cta, int*
     const long long cells = (long long)ni * nj;
     int C = 1;
     while (C < RES_MAX_CLUSTER && cells / C > 4096) C <<= 1;
+    const char* env = getenv("NSB_RES_CLUSTER");                      // tuning: smallest cluster size to try
+    if (env && atoi(env) >= 1 && atoi(env) <= RES_MAX_CLUSTER) C = atoi(env);
     for (; C <= RES_MAX_CLUSTER; C <<= 1) {
         const int R = (nj + C - 1) / C;
-        const size_t bytes = (size_t)(2 * R + 2) * w * sizeof(double);
+        // p tile + roll-back tile (R+2 rows each), RHS (R rows), final ghosts (2 (R+2) + 2 w)
+        const size_t bytes = ((size_t)(3 * R + 4) * w + 2 * (size_t)(R + 2) + 2 * (size_t)w) * sizeof(double);
         if (bytes <= RES_SMEM_LIMIT && (long long)(C - 1) * R < nj) {       // every CTA owns at least one row
             *cluster = C; *rows_per_cta = R; *W = w; *smem = bytes;
             return 1;
