@@ -12,7 +12,9 @@
  *   - stderr: accumulated SOR seconds "%.6f", no newline, last thing written (main.c:153);
  *   - unknown problem type: message + EXIT_FAILURE (main.c:105-108);
  *   - field dumps every n_print-th step to out/<n> are DISABLED in both reference mains
- *     (main.c:138-143 is commented out); set NSB_OUTPUT=1 to enable them here.
+ *     (main.c:138-143 is commented out); set NSB_OUTPUT=1 to enable them here;
+ *   - NSB_GPUS=n (n > 1) cuts the domain into n y-slabs, one per GPU of the box (new: the reference
+ *     is single-GPU).
  *
  * Plain C99, no CUDA headers: everything below the C ABI of include/nsb200.h is in libnsb200.so.
  */
@@ -31,6 +33,8 @@ int main(int argc, char* argv[])
     int n = 0, n_out = 0;
     const char* dump = getenv("NSB_OUTPUT");
     const char* verbose = getenv("NSB_VERBOSE");
+    const char* gpus_env = getenv("NSB_GPUS");
+    nsb_group* grp = NULL;
 
     if (argc > 1) param_file = argv[1];
     if (argc > 2) {
@@ -45,21 +49,26 @@ int main(int argc, char* argv[])
         printf("Unknown probem type (see parameters.txt).\n");                       /* main.c:106 */
         exit(EXIT_FAILURE);
     }
-    if (nsb_create(&P, NULL, &ctx) != NSB_OK) {
+    if (gpus_env && atoi(gpus_env) > 1) {                                            /* y-slabs over NSB_GPUS devices */
+        if (nsb_group_create(&P, NULL, atoi(gpus_env), NULL, &grp) != NSB_OK) {
+            fprintf(stderr, "CUDA error: %s\n", nsb_group_last_error(NULL));
+            exit(EXIT_FAILURE);
+        }
+    } else if (nsb_create(&P, NULL, &ctx) != NSB_OK) {
         fprintf(stderr, "CUDA error: %s\n", nsb_last_error(NULL));                   /* main.cu:36-43 */
         exit(EXIT_FAILURE);
     }
     while (t < P.T) {                                                                /* main.c:86 */
         nsb_step_info info;
-        int rc = nsb_step(ctx, t, &info);
+        int rc = grp ? nsb_group_step(grp, t, &info) : nsb_step(ctx, t, &info);
         if (rc != NSB_OK) {
-            fprintf(stderr, "CUDA error: %s\n", nsb_last_error(ctx));
+            fprintf(stderr, "CUDA error: %s\n", grp ? nsb_group_last_error(grp) : nsb_last_error(ctx));
             exit(EXIT_FAILURE);
         }
         if (verbose)
             fprintf(stderr, "step %d t %.10g dt %.10g umax %.6g vmax %.6g gamma %.6g normp %.6g its %d res %.6g\n",
                     n, info.t, info.dt, info.u_max, info.v_max, info.gamma, info.norm_p, info.sor_iters, info.res);
-        if (dump && dump[0] == '1' && P.n_print > 0 && n % P.n_print == 0) {         /* main.c:138-143 */
+        if (!grp && dump && dump[0] == '1' && P.n_print > 0 && n % P.n_print == 0) { /* main.c:138-143 */
             char prefix[64];
             snprintf(prefix, sizeof prefix, "out/%d", n_out);
             if (nsb_output(ctx, t, prefix) != NSB_OK) {
@@ -74,12 +83,14 @@ int main(int argc, char* argv[])
     }
     {
         double uc = 0.0, vc = 0.0;
-        nsb_get_center(ctx, &uc, &vc);
+        if (grp) nsb_group_get_center(grp, &uc, &vc);
+        else nsb_get_center(ctx, &uc, &vc);
         printf("U-CENTER: %.6f\n", uc);                                              /* main.c:148 */
         printf("V-CENTER: %.6f\n", vc);                                              /* main.c:149 */
     }
     fflush(stdout);
-    fprintf(stderr, "%.6f", nsb_sor_seconds(ctx));                                   /* main.c:153 */
-    nsb_destroy(ctx);
+    fprintf(stderr, "%.6f", grp ? nsb_group_sor_seconds(grp) : nsb_sor_seconds(ctx)); /* main.c:153 */
+    if (grp) nsb_group_destroy(grp);
+    else nsb_destroy(ctx);
     return 0;
 }
