@@ -125,7 +125,7 @@ int nsb_apply_bc(nsb_ctx* ctx, double t);
 int nsb_fg(nsb_ctx* ctx, double dt, double gamma);
 /* main.c:116-120; replaces calculate_RHS_kernel main.cu:219-229 */
 int nsb_rhs(nsb_ctx* ctx, double dt);
-/* fused F,G,RHS (one pass over u,v) */
+/* F, G and RHS in one call (nsb_fg then nsb_rhs) */
 int nsb_fg_rhs(nsb_ctx* ctx, double dt, double gamma);
 /* integration.h:165 SOR() in the order of SOR_UVA_with_shared_memory main.cu:656-726.
  * Returns it+1 (>0) when converged, NSB_NOT_CONVERGED after max_it, other negatives on error.

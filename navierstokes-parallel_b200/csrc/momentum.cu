@@ -204,87 +204,15 @@ cudaError_t nsb_launch_rhs(nsb_ctx* c, double dt) {
     return NSB_LAUNCHED(c, 1);
 }
 
-// ------------------------------------------------------------------ fused F, G, RHS: one pass over u, v
-// Tile of FT_X x FT_Y cells per block.  Every thread computes F and G of its cells (same f_cell / g_cell
-// as the separate kernels: same bits), stores them and parks them in shared memory together with the
-// one extra column F(i0-1, .) and the one extra row G(., j0-1) the right-hand side needs (recomputed:
-// +1/128 of F, +1/16 of G), then RHS = 1/dt ((F - F_w)/dx + (G - G_s)/dy) comes from shared memory.
-// Algorithmic traffic 40 B per cell (u, v in; F, G, RHS out) instead of 32 + 24 for the two kernels.
-// Wall values F(0,.), F(i_max,.), G(.,0), G(.,j_max) are never computed (integration.c:76,84): they are
-// READ, like the reference's RHS loop reads what calloc left there.
-#define FT_X 128
-#define FT_Y 16
-#define FT_TY 4
-
-template <bool RECIP, bool RECIPD>
-__global__ void __launch_bounds__(FT_X* FT_TY) fgrhs_kernel(const double* __restrict__ u, const double* __restrict__ v,
-                                                            double* __restrict__ F, double* __restrict__ G,
-                                                            double* __restrict__ rhs, long long pitch, int ni, int nj,
-                                                            int g_hi, int g_lo, MomCoef m) {
-    __shared__ double sF[FT_Y][FT_X + 1];      // [.][0] = column i0 - 1
-    __shared__ double sG[FT_Y + 1][FT_X];      // [0][.] = row j0 - 1
-    const int tx = threadIdx.x, ty = threadIdx.y;
-    const int i = blockIdx.x * FT_X + tx + 1;
-    const int j0 = blockIdx.y * FT_Y + 1;
-#pragma unroll
-    for (int k = 0; k < FT_Y / FT_TY; k++) {
-        const int jj = ty + FT_TY * k, j = j0 + jj;
-        if (i <= ni && j <= nj) {
-            const long long o = (long long)(j + NSB_ROW0) * pitch + NSB_COL0 + i;
-            double f, g;
-            if (i <= ni - 1) { f = f_cell<RECIP>(u, v, o, pitch, m); F[o] = f; } else f = F[o];
-            if (j <= g_hi) { g = g_cell<RECIP>(u, v, o, pitch, m); G[o] = g; } else g = G[o];
-            sF[jj][tx + 1] = f;
-            sG[jj + 1][tx] = g;
-            if (tx == 0) sF[jj][0] = (i - 1 >= 1) ? f_cell<RECIP>(u, v, o - 1, pitch, m) : F[o - 1];
-            if (jj == 0) sG[0][tx] = (j - 1 >= g_lo) ? g_cell<RECIP>(u, v, o - pitch, pitch, m) : G[o - pitch];
-        }
-    }
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < FT_Y / FT_TY; k++) {
-        const int jj = ty + FT_TY * k, j = j0 + jj;
-        if (i <= ni && j <= nj) {
-            const long long o = (long long)(j + NSB_ROW0) * pitch + NSB_COL0 + i;
-            rhs[o] = rhs_cell<RECIPD>(sF[jj][tx + 1], sF[jj][tx], sG[jj + 1][tx], sG[jj][tx], m);
-        }
-    }
-}
-
-__global__ void rhs_row_kernel(const double* __restrict__ F, const double* __restrict__ G, double* __restrict__ rhs,
-                               long long pitch, int ni, int j, MomCoef m, int recipd) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
-    if (i > ni) return;
-    const long long o = (long long)(j + NSB_ROW0) * pitch + NSB_COL0 + i;
-    rhs[o] = recipd ? rhs_cell<true>(F[o], F[o - 1], G[o], G[o - pitch], m) : rhs_cell<false>(F[o], F[o - 1], G[o], G[o - pitch], m);
-}
-
-// F, G and RHS in one pass.  On a slab that does not start at the bottom wall the row below its first row
-// belongs to the neighbour: its G arrives with the halo exchange, and nsb_launch_rhs_first_row() redoes
-// the right-hand side of local row 1 after that.
+// F, G, then RHS.  (A fused single-pass kernel -- 128 x 16 tile, F and G parked in shared memory with a
+// recomputed halo column / row, 40 instead of 56 B per cell -- was measured at 928 us against 589 + 278 us
+// for the two kernels at 8192^2: the stencils are instruction-issue bound (~200 instructions per cell
+// in the non-contracting reference arithmetic), not HBM bound, and the fused body's register pressure
+// halves the occupancy.  profiles/r1f_ncu_summary.txt.)
 cudaError_t nsb_launch_fg_rhs(nsb_ctx* c, double dt, double gamma) {
-    MomCoef m = make_mom(c, dt, gamma);
-    dim3 b(FT_X, FT_TY), g((c->g.ni + FT_X - 1) / FT_X, (c->g.nj + FT_Y - 1) / FT_Y);
-    const int g_hi = c->wall_top ? c->g.nj - 1 : c->g.nj;
-    const int g_lo = 1;     // row 0 is never recomputed: at the bottom wall it is the stored wall value, on a slab
-                            // boundary the neighbour's row (the u, v halo is one row deep -- not enough to redo it)
-    const bool rd = (c->O.div_mode == NSB_DIV_RECIP) || (c->O.div_mode == NSB_DIV_AUTO && pow2(c->dx) && pow2(c->dy));
-    const bool r2 = c->use_recip;
-#define FGRHS(A, B) fgrhs_kernel<A, B><<<g, b, 0, c->stream>>>(c->u, c->v, c->F, c->G, c->rhs, c->g.pitch, c->g.ni, c->g.nj, g_hi, g_lo, m)
-    if (r2 && rd) FGRHS(true, true);
-    else if (r2) FGRHS(true, false);
-    else if (rd) FGRHS(false, true);
-    else FGRHS(false, false);
-#undef FGRHS
-    return NSB_LAUNCHED(c, 1);
-}
-
-cudaError_t nsb_launch_rhs_first_row(nsb_ctx* c, double dt) {
-    if (c->wall_bottom) return cudaSuccess;
-    MomCoef m = make_mom(c, dt, 0.0);
-    const bool rd = (c->O.div_mode == NSB_DIV_RECIP) || (c->O.div_mode == NSB_DIV_AUTO && pow2(c->dx) && pow2(c->dy));
-    rhs_row_kernel<<<(c->g.ni + 255) / 256, 256, 0, c->stream>>>(c->F, c->G, c->rhs, c->g.pitch, c->g.ni, 1, m, rd ? 1 : 0);
-    return NSB_LAUNCHED(c, 1);
+    cudaError_t e = nsb_launch_fg(c, dt, gamma);
+    if (e != cudaSuccess) return e;
+    return nsb_launch_rhs(c, dt);
 }
 
 // ------------------------------------------------------------------ velocity update + reductions

@@ -185,8 +185,7 @@ static inline size_t nsb_index(const NsbGrid& g, int i, int j) {
 cudaError_t nsb_launch_set_inflow(nsb_ctx* c, int side, double u_fix, double v_fix);
 cudaError_t nsb_launch_fg(nsb_ctx* c, double dt, double gamma);
 cudaError_t nsb_launch_rhs(nsb_ctx* c, double dt);
-cudaError_t nsb_launch_fg_rhs(nsb_ctx* c, double dt, double gamma);   // fused: one pass over u, v
-cudaError_t nsb_launch_rhs_first_row(nsb_ctx* c, double dt);           // slabs: local row 1 after the G halo arrived
+cudaError_t nsb_launch_fg_rhs(nsb_ctx* c, double dt, double gamma);
 cudaError_t nsb_launch_update_uv(nsb_ctx* c, double dt);
 cudaError_t nsb_launch_reduce_uvp(nsb_ctx* c);     // max u, max v, sum p^2 without updating
 cudaError_t nsb_launch_sor_begin(nsb_ctx* c);      // threshold from sum p^2, clears the flags

@@ -306,10 +306,10 @@ static int step_ranks(nsb_ctx** cs, int n, double t, nsb_step_info* info) {
     ALL(nsb_ph_bc(c, t));                                      // main.c:95-108
     ALLCU(nsb_launch_halo_push(c, NSB_X_UV));
     ALLCU(nsb_launch_halo_wait(c, NSB_X_UV));
-    ALLCU(nsb_launch_fg_rhs(c, dt, gamma));                    // main.c:112 and :116-120 in one pass over u, v
+    ALLCU(nsb_launch_fg(c, dt, gamma));                        // main.c:112
     ALLCU(nsb_launch_halo_push(c, NSB_X_G));
     ALLCU(nsb_launch_halo_wait(c, NSB_X_G));
-    ALLCU(nsb_launch_rhs_first_row(c, dt));                    // slabs: the row whose G_s came from the neighbour
+    ALLCU(nsb_launch_rhs(c, dt));                              // main.c:116-120
     ALLCU(nsb_launch_halo_push(c, NSB_X_RHS));
     ALLCU(nsb_launch_halo_wait(c, NSB_X_RHS));
     if ((r = sor_solve(cs, n, c0->P.max_it, 1))) return r;     // main.c:123
