@@ -18,6 +18,7 @@
 // block (fixed tree) and over the CTAs in rank order: deterministic, but not the summation order of
 // the streaming engine -- only the convergence test sees it.
 #include <cooperative_groups.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -178,10 +179,18 @@ __global__ void __launch_bounds__(RES_THREADS, 1) sor_resident_kernel(const Resi
     // values in B and is rolled back if iteration n turns out to have converged.
     int it = 0, converged = 0;
     double res = a.ctl->res, total = a.ctl->sum_r2;
+#ifdef RES_TIMING
+    long long tk[8];
+#define TICK(n) tk[n] = clock64()
+#else
+#define TICK(n)
+#endif
     for (;; it++) {
         const bool real = it < a.max_it;
+        TICK(0);
         if (real) {
             resident_pass<RECIP, 0>(P, Q, B, gf, W, R, ni, nj, jlo, 0, false, a.k, tx, ty, TX, TY);
+            TICK(1);
             __syncthreads();
             if (has_down)                                               // my row l = 1 -> their row R_down + 1 (cells of colour 0)
                 for (int i = 1 + ((jlo + 1) & 1) + 2 * tid; i <= ni; i += 2 * RES_THREADS)
@@ -190,7 +199,9 @@ __global__ void __launch_bounds__(RES_THREADS, 1) sor_resident_kernel(const Resi
                 for (int i = 1 + ((jlo + R) & 1) + 2 * tid; i <= ni; i += 2 * RES_THREADS)
                     Pup[i + 1] = P[(size_t)R * W + i + 1];
         }
-        cluster.sync();
+        TICK(2);
+        if (C > 1) cluster.sync(); else __syncthreads();
+        TICK(3);
         if (it > 0) {                                                   // close iteration it-1 (every thread, same order)
             double t = 0.0;
             for (int r = 0; r < C; r++) t += parts[r];
@@ -204,7 +215,9 @@ __global__ void __launch_bounds__(RES_THREADS, 1) sor_resident_kernel(const Resi
             __syncthreads();
             break;
         }
+        TICK(4);
         double acc = resident_pass<RECIP, 0>(P, Q, nullptr, gf, W, R, ni, nj, jlo, 1, true, a.k, tx, ty, TX, TY);
+        TICK(5);
         __syncthreads();
         if (has_down)
             for (int i = 1 + ((jlo + 2) & 1) + 2 * tid; i <= ni; i += 2 * RES_THREADS)
@@ -212,12 +225,19 @@ __global__ void __launch_bounds__(RES_THREADS, 1) sor_resident_kernel(const Resi
         if (has_up)
             for (int i = 1 + ((jlo + R + 1) & 1) + 2 * tid; i <= ni; i += 2 * RES_THREADS)
                 Pup[i + 1] = P[(size_t)R * W + i + 1];
-        cluster.sync();
+        if (C > 1) cluster.sync(); else __syncthreads();
+        TICK(6);
         // residual of the cells of colour 0: their neighbours are final now; ghosts next to them hold their own value
         acc += resident_pass<RECIP, 1>(P, Q, nullptr, gf, W, R, ni, nj, jlo, 0, false, a.k, tx, ty, TX, TY);
         const double bsum = block_sum(acc, red_sh);
         if (tid == 0)
             for (int r = 0; r < C; r++) cluster.map_shared_rank(parts, r)[rank] = bsum;
+#ifdef RES_TIMING
+        TICK(7);
+        if (it == 7 && tid == 0 && (rank == 0 || rank == C / 2))
+            printf("rank %d: red %lld sync+push %lld csync %lld close %lld black %lld sync+push+csync %lld redres+sum %lld total %lld\n", rank,
+                   tk[1] - tk[0], tk[2] - tk[1], tk[3] - tk[2], tk[4] - tk[3], tk[5] - tk[4], tk[6] - tk[5], tk[7] - tk[6], tk[7] - tk[0]);
+#endif
         // (visible to every CTA after the next cluster barrier; rewritten only two barriers later)
     }
     // `it` iterations are complete and closed

@@ -878,15 +878,14 @@ cudaError_t nsb_launch_sor_close(nsb_ctx* c, int it, int check) {
 
 // ------------------------------------------------------------------------------------------
 // Planning: strips are fixed (120 columns); pick an even chunk height that fills whole waves.
-static int g_attr_done = 0;
 
 void nsb_sor_plan(nsb_ctx* c) {
     const int ni = c->g.ni, nj = c->g.nj;
-    if (!g_attr_done) {
-        cudaFuncSetAttribute(sor_stream_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES);
-        cudaFuncSetAttribute(sor_stream_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES);
-        g_attr_done = 1;
-    }
+    // function attributes are per device: set them for the device of every context that is planned
+    cudaFuncSetAttribute(sor_stream_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES);
+    cudaFuncSetAttribute(sor_stream_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES);
+    cudaFuncSetAttribute(sor_persist_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES);
+    cudaFuncSetAttribute(sor_persist_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES);
     c->n_strips = (ni + NSB_STRIP_COLS - 1) / NSB_STRIP_COLS;
     int blocks_per_sm = 0;
     if (c->use_recip)
@@ -1019,12 +1018,6 @@ cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int n_iter, int check) {
     pa.claim = c->d_claim; pa.done = c->d_done; pa.partials2 = c->d_partials2;
     pa.flag_base = c->flag_base;
     c->flag_base += (unsigned long long)n_iter + 1ull;
-    static int attr_done = 0;
-    if (!attr_done) {
-        cudaFuncSetAttribute(sor_persist_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES);
-        cudaFuncSetAttribute(sor_persist_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES);
-        attr_done = 1;
-    }
     int bps = 0;
     if (c->use_recip) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sor_persist_kernel<true>, SOR_THREADS, SOR_SMEM_BYTES);
     else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sor_persist_kernel<false>, SOR_THREADS, SOR_SMEM_BYTES);
