@@ -41,6 +41,10 @@ struct ResidentArgs {
     int max_it, check, it0;
     SorCoef k;
     SorCtl* ctl;
+    // cooperative-grid variant (tiles spread over up to all SMs): boundary rows and block partials
+    // travel through HBM/L2 instead of distributed shared memory
+    double* ghalo;             // [n_cta][2][W]: [.][0] = first interior row, [.][1] = last interior row of the CTA
+    double* gparts;            // [n_cta]
 };
 
 // Final ghost values as the reference leaves them (the refresh before the LAST black sweep,
@@ -124,14 +128,58 @@ __device__ __forceinline__ void resident_ghosts(double* P, const GhostFinal& gf,
         }
 }
 
-template <bool RECIP>
+// Boundary rows to the neighbours after a colour pass: only the cells of that colour changed.
+// Cluster: straight into the neighbour's halo row (DSMEM).  Grid: into this CTA's global halo slot.
+template <bool GRID>
+__device__ __forceinline__ void resident_push(const double* P, double* Pdown, double* Pup, double* hmine, int W, int R,
+                                              int R_down, int ni, int jlo, int color, bool has_down, bool has_up, int tid) {
+    const int i_dn = 1 + ((jlo + 1 + color) & 1);            // first cell of this colour in my row l = 1 (global row jlo)
+    const int i_up = 1 + ((jlo + R + color) & 1);            // ... in my row l = R (global row jlo + R - 1)
+    if (has_down)
+        for (int i = i_dn + 2 * tid; i <= ni; i += 2 * RES_THREADS) {
+            if (GRID) hmine[i + 1] = P[(size_t)W + i + 1];
+            else Pdown[(size_t)(R_down + 1) * W + i + 1] = P[(size_t)W + i + 1];
+        }
+    if (has_up)
+        for (int i = i_up + 2 * tid; i <= ni; i += 2 * RES_THREADS) {
+            if (GRID) hmine[W + i + 1] = P[(size_t)R * W + i + 1];
+            else Pup[i + 1] = P[(size_t)R * W + i + 1];
+        }
+}
+
+// Grid variant, after the barrier: fetch the neighbours' boundary cells of that colour into my halo rows.
+__device__ __forceinline__ void resident_pull(double* P, const double* ghalo, int W, int R, int ni, int jlo, int color,
+                                              int rank, bool has_down, bool has_up, int tid) {
+    if (has_down) {                                          // row below me = global row jlo - 1 = last row of rank - 1
+        const double* h = ghalo + ((size_t)(rank - 1) * 2 + 1) * W;
+        for (int i = 1 + ((jlo + color) & 1) + 2 * tid; i <= ni; i += 2 * RES_THREADS) P[i + 1] = __ldcg(h + i + 1);
+    }
+    if (has_up) {                                            // row above me = global row jlo + R = first row of rank + 1
+        const double* h = ghalo + (size_t)(rank + 1) * 2 * W;
+        for (int i = 1 + ((jlo + R + 1 + color) & 1) + 2 * tid; i <= ni; i += 2 * RES_THREADS)
+            P[(size_t)(R + 1) * W + i + 1] = __ldcg(h + i + 1);
+    }
+}
+
+// Barrier over all CTAs of the solve: hardware cluster barrier, or the cooperative grid barrier.
+template <bool GRID>
+__device__ __forceinline__ void resident_sync(int C) {
+    if (GRID) cg::this_grid().sync();
+    else if (C > 1) cg::this_cluster().sync();
+    else __syncthreads();
+}
+
+// GRID = false: one thread-block cluster (<= 16 CTAs), halos and partials through distributed shared memory.
+// GRID = true : cooperative launch over up to one CTA per SM, halos and partials through global memory
+//               (grids up to ~1024^2; per iteration two grid barriers instead of two cluster barriers).
+template <bool RECIP, bool GRID>
 __global__ void __launch_bounds__(RES_THREADS, 1) sor_resident_kernel(const ResidentArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ double red_sh[32];
     __shared__ double parts[RES_MAX_CLUSTER];
-    cg::cluster_group cluster = cg::this_cluster();
-    const int C = (int)cluster.num_blocks();
-    const int rank = (int)cluster.block_rank();
+    __shared__ double tot_sh;
+    const int C = GRID ? (int)gridDim.x : (int)cg::this_cluster().num_blocks();
+    const int rank = GRID ? (int)blockIdx.x : (int)cg::this_cluster().block_rank();
     const int W = a.W, ni = a.ni, nj = a.nj;
     const int jlo = 1 + rank * a.rows_per_cta;                         // first global row of this CTA
     const int R = min(a.rows_per_cta, nj - jlo + 1);                   // >= 1 by construction (resident_plan)
@@ -157,9 +205,10 @@ __global__ void __launch_bounds__(RES_THREADS, 1) sor_resident_kernel(const Resi
         const long long ro = (long long)(jlo - 1 + l) * a.pitch;
         for (int i = tid; i <= ni + 1; i += RES_THREADS) Q[(size_t)(l - 1) * W + i + 1] = gq[ro + i];
     }
-    // neighbours' tiles through distributed shared memory
-    double* Pdown = (rank > 0) ? cluster.map_shared_rank(P, rank - 1) : nullptr;
-    double* Pup = (rank + 1 < C) ? cluster.map_shared_rank(P, rank + 1) : nullptr;
+    // neighbours' tiles through distributed shared memory (cluster variant)
+    double* Pdown = (!GRID && rank > 0) ? cg::this_cluster().map_shared_rank(P, rank - 1) : nullptr;
+    double* Pup = (!GRID && rank + 1 < C) ? cg::this_cluster().map_shared_rank(P, rank + 1) : nullptr;
+    double* hmine = GRID ? a.ghalo + (size_t)rank * 2 * W : nullptr;
     const int R_down = a.rows_per_cta;                                // every CTA below the last one is full
     const bool has_up = (rank + 1 < C) && (jlo + R <= nj);
     const bool has_down = (rank > 0);
@@ -172,7 +221,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) sor_resident_kernel(const Resi
     __syncthreads();
     resident_ghosts(P, gf, W, R, ni, first, last);                                       // main.cu:686 of iteration 0
     __syncthreads();
-    cluster.sync();
+    resident_sync<GRID>(C);
 
     // Per iteration two cluster barriers.  The partial sums of iteration n become visible at the first
     // barrier of iteration n+1, i.e. after its first colour has already run: that colour keeps the old
@@ -192,19 +241,26 @@ __global__ void __launch_bounds__(RES_THREADS, 1) sor_resident_kernel(const Resi
             resident_pass<RECIP, 0>(P, Q, B, gf, W, R, ni, nj, jlo, 0, false, a.k, tx, ty, TX, TY);
             TICK(1);
             __syncthreads();
-            if (has_down)                                               // my row l = 1 -> their row R_down + 1 (cells of colour 0)
-                for (int i = 1 + ((jlo + 1) & 1) + 2 * tid; i <= ni; i += 2 * RES_THREADS)
-                    Pdown[(size_t)(R_down + 1) * W + i + 1] = P[(size_t)W + i + 1];
-            if (has_up)                                                 // my row l = R -> their row 0
-                for (int i = 1 + ((jlo + R) & 1) + 2 * tid; i <= ni; i += 2 * RES_THREADS)
-                    Pup[i + 1] = P[(size_t)R * W + i + 1];
+            resident_push<GRID>(P, Pdown, Pup, hmine, W, R, R_down, ni, jlo, 0, has_down, has_up, tid);
         }
         TICK(2);
-        if (C > 1) cluster.sync(); else __syncthreads();
+        resident_sync<GRID>(C);
+        if (GRID && real) { resident_pull(P, a.ghalo, W, R, ni, jlo, 0, rank, has_down, has_up, tid); __syncthreads(); }
         TICK(3);
-        if (it > 0) {                                                   // close iteration it-1 (every thread, same order)
+        if (it > 0) {                                                   // close iteration it-1 (every CTA, same order)
             double t = 0.0;
-            for (int r = 0; r < C; r++) t += parts[r];
+            if (GRID) {
+                if (tid < 32) {
+                    double q = 0.0;
+                    for (int r = tid; r < C; r += 32) q += __ldcg(a.gparts + r);
+                    q = warp_sum(q);
+                    if (tid == 0) tot_sh = q;
+                }
+                __syncthreads();
+                t = tot_sh;
+            } else {
+                for (int r = 0; r < C; r++) t += parts[r];
+            }
             total = t;
             res = sqrt(t / (double)a.k.cells);                          // main.cu:588
             converged = (res <= thresh) ? 1 : 0;                        // main.cu:713
@@ -219,19 +275,17 @@ __global__ void __launch_bounds__(RES_THREADS, 1) sor_resident_kernel(const Resi
         double acc = resident_pass<RECIP, 0>(P, Q, nullptr, gf, W, R, ni, nj, jlo, 1, true, a.k, tx, ty, TX, TY);
         TICK(5);
         __syncthreads();
-        if (has_down)
-            for (int i = 1 + ((jlo + 2) & 1) + 2 * tid; i <= ni; i += 2 * RES_THREADS)
-                Pdown[(size_t)(R_down + 1) * W + i + 1] = P[(size_t)W + i + 1];
-        if (has_up)
-            for (int i = 1 + ((jlo + R + 1) & 1) + 2 * tid; i <= ni; i += 2 * RES_THREADS)
-                Pup[i + 1] = P[(size_t)R * W + i + 1];
-        if (C > 1) cluster.sync(); else __syncthreads();
+        resident_push<GRID>(P, Pdown, Pup, hmine, W, R, R_down, ni, jlo, 1, has_down, has_up, tid);
+        resident_sync<GRID>(C);
+        if (GRID) { resident_pull(P, a.ghalo, W, R, ni, jlo, 1, rank, has_down, has_up, tid); __syncthreads(); }
         TICK(6);
         // residual of the cells of colour 0: their neighbours are final now; ghosts next to them hold their own value
         acc += resident_pass<RECIP, 1>(P, Q, nullptr, gf, W, R, ni, nj, jlo, 0, false, a.k, tx, ty, TX, TY);
         const double bsum = block_sum(acc, red_sh);
-        if (tid == 0)
-            for (int r = 0; r < C; r++) cluster.map_shared_rank(parts, r)[rank] = bsum;
+        if (tid == 0) {
+            if (GRID) a.gparts[rank] = bsum;
+            else for (int r = 0; r < C; r++) cg::this_cluster().map_shared_rank(parts, r)[rank] = bsum;
+        }
 #ifdef RES_TIMING
         TICK(7);
         if (it == 7 && tid == 0 && (rank == 0 || rank == C / 2))
@@ -265,64 +319,104 @@ __global__ void __launch_bounds__(RES_THREADS, 1) sor_resident_kernel(const Resi
 }
 
 // ------------------------------------------------------------------------------------------ host
-static int resident_plan(const nsb_ctx* c, int* cluster, int* rows_per_cta, int* W, size_t* smem) {
+struct ResidentPlan {
+    int n_cta, rows_per_cta, W, grid;   // grid = 1: cooperative-grid variant, 0: one cluster
+    size_t smem;
+};
+
+static size_t resident_bytes(int R, int w) {
+    // p tile + roll-back tile (R+2 rows each), RHS (R rows), final ghosts (2 (R+2) + 2 w)
+    return ((size_t)(3 * R + 4) * w + 2 * (size_t)(R + 2) + 2 * (size_t)w) * sizeof(double);
+}
+
+static int resident_plan(const nsb_ctx* c, ResidentPlan* pl) {
     if (c->world != 1) return 0;
     const int ni = c->g.ni, nj = c->g.nj;
     const int w = (ni + 3 + 1) & ~1;
     const long long cells = (long long)ni * nj;
+    pl->W = w;
+    const char* mode = getenv("NSB_RES_MODE");                        // tuning: "grid" / "cluster" forces a variant
+    const bool force_grid = mode && mode[0] == 'g', force_cluster = mode && mode[0] == 'c';
+    // one cluster: up to 16 CTAs
     int C = 1;
     while (C < RES_MAX_CLUSTER && cells / C > 4096) C <<= 1;
     const char* env = getenv("NSB_RES_CLUSTER");                      // tuning: smallest cluster size to try
     if (env && atoi(env) >= 1 && atoi(env) <= RES_MAX_CLUSTER) C = atoi(env);
-    for (; C <= RES_MAX_CLUSTER; C <<= 1) {
+    for (; C <= RES_MAX_CLUSTER && !force_grid; C <<= 1) {
         const int R = (nj + C - 1) / C;
-        // p tile + roll-back tile (R+2 rows each), RHS (R rows), final ghosts (2 (R+2) + 2 w)
-        const size_t bytes = ((size_t)(3 * R + 4) * w + 2 * (size_t)(R + 2) + 2 * (size_t)w) * sizeof(double);
-        if (bytes <= RES_SMEM_LIMIT && (long long)(C - 1) * R < nj) {       // every CTA owns at least one row
-            *cluster = C; *rows_per_cta = R; *W = w; *smem = bytes;
+        if (resident_bytes(R, w) <= RES_SMEM_LIMIT && (long long)(C - 1) * R < nj) {   // every CTA owns at least one row
+            pl->n_cta = C; pl->rows_per_cta = R; pl->smem = resident_bytes(R, w); pl->grid = 0;
             return 1;
         }
     }
-    return 0;
+    if (force_cluster) return 0;
+    // cooperative grid: up to one CTA per SM
+    int G = c->sm_count < nj ? c->sm_count : nj;
+    const long long fit = (long long)(c->g.elems / (size_t)(2 * w + 1));   // halo rows + partials live in the scratch grid
+    if (G > fit) G = (int)fit;
+    if (G < 1) return 0;
+    const int R = (nj + G - 1) / G;
+    G = (nj + R - 1) / R;
+    if (resident_bytes(R, w) > RES_SMEM_LIMIT) return 0;
+    pl->n_cta = G; pl->rows_per_cta = R; pl->smem = resident_bytes(R, w); pl->grid = 1;
+    return 1;
 }
 
-static int g_resident_state = 0;   // 0 unknown, 1 usable, -1 the device refused a cluster launch
+static int g_resident_state = 0;   // 0 unknown, 1 usable, -1 the device refused the launch
 
 int nsb_sor_resident_supported(const nsb_ctx* c) {
     if (g_resident_state < 0) return 0;
-    int C, R, W; size_t smem;
-    return resident_plan(c, &C, &R, &W, &smem);
+    ResidentPlan pl;
+    return resident_plan(c, &pl);
 }
 
 cudaError_t nsb_launch_sor_resident(nsb_ctx* c, int max_it, int check) {
-    int C, R, W; size_t smem;
-    if (!resident_plan(c, &C, &R, &W, &smem)) return cudaErrorNotSupported;
+    ResidentPlan pl;
+    if (!resident_plan(c, &pl)) return cudaErrorNotSupported;
     ResidentArgs a;
     memset(&a, 0, sizeof a);
     a.p = c->pbuf[c->pcur]; a.rhs = c->rhs; a.pitch = c->g.pitch; a.ni = c->g.ni; a.nj = c->g.nj;
-    a.W = W; a.rows_per_cta = R; a.max_it = max_it; a.check = check; a.it0 = 0;
+    a.W = pl.W; a.rows_per_cta = pl.rows_per_cta; a.max_it = max_it; a.check = check; a.it0 = 0;
     const double dx2 = c->dx * c->dx, dy2 = c->dy * c->dy;
     a.k.om1 = 1.0 - c->P.omega;
     a.k.w = c->P.omega / (2.0 * (1.0 / dx2 + 1.0 / dy2));
     a.k.dx2 = dx2; a.k.dy2 = dy2; a.k.rdx2 = 1.0 / dx2; a.k.rdy2 = 1.0 / dy2;
     a.k.cells = (long long)c->g.ni * (long long)c->J;
     a.ctl = c->d_ctl;
-    auto kern = c->use_recip ? sor_resident_kernel<true> : sor_resident_kernel<false>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e;
+    if (pl.grid) {
+        // halo rows + partials in HBM: the scratch grid is free during a solve
+        a.ghalo = c->scratch;
+        a.gparts = c->scratch + (size_t)pl.n_cta * 2 * pl.W;
+        if (((size_t)pl.n_cta * 2 * pl.W + pl.n_cta) > c->g.elems) return cudaErrorNotSupported;
+        const void* kern = c->use_recip ? (const void*)sor_resident_kernel<true, true> : (const void*)sor_resident_kernel<false, true>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
+        if (e != cudaSuccess) return e;
+        int occ = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, RES_THREADS, pl.smem);
+        if (occ * c->sm_count < pl.n_cta) { g_resident_state = -1; return cudaErrorNotSupported; }
+        void* args[] = {&a};
+        e = cudaLaunchCooperativeKernel(kern, dim3(pl.n_cta), dim3(RES_THREADS), args, pl.smem, c->stream);
+        if (e != cudaSuccess) { g_resident_state = -1; cudaGetLastError(); return e; }
+        g_resident_state = 1;
+        return NSB_LAUNCHED(c, 1);
+    }
+    auto kern = c->use_recip ? sor_resident_kernel<true, false> : sor_resident_kernel<false, false>;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
     if (e != cudaSuccess) return e;
-    if (C > 8) {
+    if (pl.n_cta > 8) {
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
         if (e != cudaSuccess) return e;
     }
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof cfg);
-    cfg.gridDim = dim3(C, 1, 1);
+    cfg.gridDim = dim3(pl.n_cta, 1, 1);
     cfg.blockDim = dim3(RES_THREADS, 1, 1);
-    cfg.dynamicSmemBytes = smem;
+    cfg.dynamicSmemBytes = pl.smem;
     cfg.stream = c->stream;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = C; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[0].val.clusterDim.x = pl.n_cta; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
     e = cudaLaunchKernelEx(&cfg, kern, a);
     if (e != cudaSuccess) { g_resident_state = -1; cudaGetLastError(); return e; }

@@ -126,6 +126,45 @@ def test_sor_per_iteration_bit_exact(engine, ni, nj):
     s.close()
 
 
+@pytest.mark.parametrize("ni,nj", [(31, 17), (257, 64), (64, 300), (600, 480)])
+def test_resident_grid_variant(ni, nj, monkeypatch):
+    """The cooperative-grid variant of the resident engine (tiles over all SMs, halos through L2), forced at
+    sizes the oracle reaches: same bits per iteration, same converged iteration count as the simple engine."""
+    m = nsb()
+    monkeypatch.setenv("NSB_RES_MODE", "grid")
+    s, P = _solver(m, engine=m.SOR_RESIDENT, i_max=ni, j_max=nj, a=1.0, b=0.9, omega=1.7, epsilon=1e-3, max_it=400)
+    L = ob.lib()
+    p = _rand(s.shape, 21) * 0.5
+    rhs = _rand(s.shape, 22) * 3.0
+    rhs -= rhs[1:-1, 1:-1].mean()
+    p0 = p.copy()
+    s.upload(m.P, p); s.upload(m.RHS, rhs)
+    dx, dy = 1.0 / ni, 0.9 / nj
+    for n in (1, 2, 5):
+        r_gpu = s.sor_iterations(n)
+        for _ in range(n):
+            r_cpu = L.orc_SOR_rb_iter(ob._ptr(p), ni, nj, dx, dy, ob._ptr(rhs), P.omega)
+        got = s.download(m.P)
+        assert np.array_equal(got[1:-1, 1:-1], p[1:-1, 1:-1])
+        assert np.array_equal(got[0, 1:-1], p[0, 1:-1]) and np.array_equal(got[-1, 1:-1], p[-1, 1:-1])
+        assert np.array_equal(got[1:-1, 0], p[1:-1, 0]) and np.array_equal(got[1:-1, -1], p[1:-1, -1])
+        assert abs(r_gpu - r_cpu) <= 1e-12 * abs(r_cpu)
+    # converged solve with the roll-back of the speculative first colour: against the simple engine
+    s.upload(m.P, p0)
+    ret, its, res, n0 = s.SOR()
+    got = s.download(m.P)
+    s.close()
+    monkeypatch.delenv("NSB_RES_MODE")
+    s2, _ = _solver(m, engine=m.SOR_SIMPLE, i_max=ni, j_max=nj, a=1.0, b=0.9, omega=1.7, epsilon=1e-3, max_it=400)
+    s2.upload(m.P, p0); s2.upload(m.RHS, rhs)
+    ret2, its2, res2, n02 = s2.SOR()
+    want = s2.download(m.P)
+    s2.close()
+    assert (ret, its) == (ret2, its2)
+    assert np.array_equal(got[1:-1, 1:-1], want[1:-1, 1:-1])
+    assert np.array_equal(got[0, 1:-1], want[0, 1:-1]) and np.array_equal(got[1:-1, 0], want[1:-1, 0])
+
+
 @pytest.mark.parametrize("div_mode", ["exact", "recip"])
 def test_sor_division_modes(div_mode):
     """Non power-of-two spacing: NSB_DIV_EXACT (and AUTO) is bit-exact; NSB_DIV_RECIP stays within
