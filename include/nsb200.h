@@ -60,7 +60,8 @@ enum {
     NSB_SOR_STREAM = 1,   /* fused red+black+residual streaming pass; on a single slab ALL iterations of a
                              solve run in one persistent launch (tasks of iteration n+1 start as soon as
                              their neighbours of iteration n are done), on y-slabs one launch per iteration */
-    NSB_SOR_RESIDENT = 2, /* grid held on-chip by one thread-block cluster, all iterations in one launch */
+    NSB_SOR_RESIDENT = 2, /* grid held in shared memory (one thread-block cluster, or one CTA per SM for grids
+                             up to ~1024^2), all iterations in one launch; falls back to the stream engine */
     NSB_SOR_SIMPLE = 3,   /* one launch per colour + residual launch (validation kernel)        */
     NSB_SOR_STREAM_LAUNCH = 4 /* the streaming pass with one launch per iteration on a single slab too */
 };

@@ -1,21 +1,28 @@
-// sor_resident.cu -- cluster-resident SOR engine for grids that fit on chip: p and RHS of the whole
-// grid live in the shared memory of ONE thread-block cluster (up to 16 SMs), all iterations of a
-// solve run inside one launch, neighbouring CTAs exchange their boundary rows through distributed
-// shared memory and synchronise with the hardware cluster barrier.
+// sor_resident.cu -- resident SOR engine for grids that fit on chip: p and RHS of the whole grid live
+// in shared memory, every CTA owns a band of rows, all iterations of a solve run inside one launch.
+//   cluster variant : ONE thread-block cluster (up to 16 SMs); boundary rows and residual partials
+//                     travel through distributed shared memory, hardware cluster barrier;
+//   grid variant    : cooperative launch, up to one CTA per SM (grids up to ~1024^2); boundary rows
+//                     and partials travel through L2, grid barrier.
 //
 // Why: at 256^2 (tests/1.in, 1 MB working set) the solve is pure latency.  The reference spends six
 // launches, six device synchronisations and a D2H copy per iteration (src/parallel/main.cu:684-719,
-// ~56 us per iteration in its published numbers); the streaming engine still pays a task hand-over
-// through L2 flags per iteration.  Here one iteration costs three cluster barriers plus the arithmetic.
+// ~56 us per iteration in its published numbers, 78 us on a B200); the streaming engine still pays a
+// task hand-over through L2 flags per iteration.  Here one iteration costs two barriers plus the
+// arithmetic: 6.5 us at 256^2, 8.7 us at 512^2, 13.5 us at 1024^2 (profiles/r1g_*).
 //
-// Order of operations = src/parallel/main.cu:684-719, with the ghost cells STORED in shared memory
-// and refreshed exactly where the reference refreshes them (before colour 0 and before colour 1, not
-// before the residual):
-//   refresh ghosts | colour 0 | exchange | refresh ghosts | colour 1 (+ residual of the black cells,
-//   whose neighbours are final) | exchange | residual of the red cells | cluster-wide sum | test.
-// Arithmetic per cell is sor_cell / sor_residual of nsb_math.cuh (reference association order, no
-// contraction): p has the same bits as every other engine.  The residual is summed per thread, per
-// block (fixed tree) and over the CTAs in rank order: deterministic, but not the summation order of
+// Order of operations = src/parallel/main.cu:684-719.  The ghost cells are STORED in shared memory;
+// the thread that owns a wall-adjacent cell lets the ghost follow its update at once, which is what
+// the reference's refresh before the NEXT colour (main.cu:686 / :694) would copy.  The residual of a
+// black cell is evaluated right after its update and BEFORE its ghost follows, so it sees the
+// pre-black value exactly like the reference (no refresh between colour 1 and the residual kernel):
+//   colour 0 | exchange + barrier | colour 1 + residual of the black cells | exchange + barrier |
+//   residual of the red cells | partials out.
+// The partial sums of iteration n are read after the first barrier of iteration n+1: its colour 0 has
+// already run by then, keeps the old values in a roll-back tile and is undone if iteration n
+// converged.  Arithmetic per cell is sor_cell / sor_residual of nsb_math.cuh (reference association
+// order, no contraction): p has the same bits as every other engine.  The residual is summed per
+// thread, per block (fixed tree) and over the CTAs in rank order: deterministic, but not the order of
 // the streaming engine -- only the convergence test sees it.
 #include <cooperative_groups.h>
 #include <stdio.h>
