@@ -208,7 +208,7 @@ cudaError_t nsb_launch_rhs(nsb_ctx* c, double dt) {
 // recomputed halo column / row, 40 instead of 56 B per cell -- was measured at 928 us against 589 + 278 us
 // for the two kernels at 8192^2: the stencils are instruction-issue bound (~200 instructions per cell
 // in the non-contracting reference arithmetic), not HBM bound, and the fused body's register pressure
-// halves the occupancy.  profiles/r1f_ncu_summary.txt.)
+// halves the occupancy.  profiles/r1g_ncu_summary.txt.)
 cudaError_t nsb_launch_fg_rhs(nsb_ctx* c, double dt, double gamma) {
     cudaError_t e = nsb_launch_fg(c, dt, gamma);
     if (e != cudaSuccess) return e;

@@ -60,3 +60,19 @@ def test_whole_run_equals_single_slab_multi_gpu(world):
         assert [x[k] for x in logg] == [x[k] for x in log1], k
     for a, b in zip(fg, f1):
         assert np.array_equal(a[1:-1, 1:-1], b[1:-1, 1:-1])
+
+
+def test_c_driver_with_nsb_gpus(tmp_path):
+    """build/parallel with NSB_GPUS=2: same stdout as the single-GPU run (the slabs are bit-identical)."""
+    import os
+    import subprocess
+    from util import ROOT
+    if _ndev() < 2:
+        pytest.skip("needs 2 GPUs")
+    exe = os.path.join(ROOT, "build", "parallel")
+    f = tmp_path / "case.in"
+    f.write_text("1\n1\n400\n384\n1.0\n1.0\n0.02\n1000.0\n0.0\n0.0\n1.0\n1.7\n0.0001\n300\n1\n")
+    one = subprocess.run([exe, str(f)], capture_output=True, text=True, timeout=300)
+    two = subprocess.run([exe, str(f)], capture_output=True, text=True, timeout=300, env=dict(os.environ, NSB_GPUS="2"))
+    assert one.returncode == 0 and two.returncode == 0, (one.stderr, two.stderr)
+    assert one.stdout == two.stdout and one.stdout.startswith("U-CENTER: ")

@@ -445,3 +445,54 @@ def test_c_driver_process_contract(tmp_path):
                 assert abs(float(a) - float(b)) <= 1e-4
             except ValueError:
                 assert a == b
+
+
+# ------------------------------------------------------------------------------- BASELINE sizes, reference binary
+
+def test_full_size_8192_engines_agree_and_nullspace():
+    """BASELINE.json configs[2] size (8192^2, beyond the CPU oracle): the persistent sweep and the
+    one-launch-per-iteration sweep give the same bits and the same residual after 6 iterations from the
+    cavity's own first right-hand side; adding a constant to p shifts the iterate by exactly that
+    constant (pure Neumann problem: constants are the null space; 0.5 is exact in binary)."""
+    m = nsb()
+    n = 8192
+    outs = []
+    for eng, shift in ((m.SOR_STREAM, 0.0), (m.SOR_STREAM_LAUNCH, 0.0), (m.SOR_STREAM, 0.5)):
+        P = m.make_params(i_max=n, j_max=n, T=1e9, max_it=3)
+        with m.Solver(P, sor_engine=eng) as s:
+            s.step(0.0)                                   # BC, F, G, RHS of the first cavity step + 3 iterations
+            if shift:
+                p = s.download(m.P, layout=m.LAYOUT_XFAST)
+                p += shift
+                s.upload(m.P, p, layout=m.LAYOUT_XFAST)
+                del p
+            r = s.sor_iterations(3)
+            outs.append((s.download(m.P, layout=m.LAYOUT_XFAST)[1:-1, 1:-1].copy(), r))
+    assert np.array_equal(outs[0][0], outs[1][0]) and outs[0][1] == outs[1][1]
+    d = outs[2][0] - outs[0][0]
+    assert np.abs(d - 0.5).max() <= 64 * np.finfo(float).eps * max(1.0, np.abs(outs[0][0]).max())
+    assert abs(outs[2][1] - outs[0][1]) <= 1e-9 * outs[0][1]
+
+
+def test_reference_cuda_binary_same_stdout(tmp_path):
+    """The reference's own CUDA build (src/parallel/*.cu compiled unmodified for sm_100 into
+    oracle/_ref/parallel by `make -C oracle refcuda`) on this GPU against build/parallel, with the
+    reference's acceptance rule (colab-runner.ipynb cell 4: stdout tokens within 1e-4).  64^2 and 128^2
+    are multiples of the block size 16 -- the only sizes the reference kernel is valid for."""
+    ref = os.path.join(ROOT, "oracle", "_ref", "parallel")
+    exe = os.path.join(ROOT, "build", "parallel")
+    if not os.path.exists(ref):
+        pytest.skip("oracle/_ref/parallel not built (make -C oracle refcuda)")
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("compare_outputs", os.path.join(ROOT, "tools", "compare_outputs.py"))
+    cmp = importlib.util.module_from_spec(spec); spec.loader.exec_module(cmp)
+    for n, T in ((64, 0.5), (128, 0.05)):
+        f = tmp_path / f"c{n}.in"
+        f.write_text(f"1\n1\n{n}\n{n}\n1.0\n1.0\n{T}\n1000.0\n0.0\n0.0\n1.0\n1.7\n0.0001\n2000\n1\n")
+        a = subprocess.run([ref, str(f), "16"], capture_output=True, text=True, timeout=300)
+        b = subprocess.run([exe, str(f), "16"], capture_output=True, text=True, timeout=300)
+        assert a.returncode == 0 and b.returncode == 0, (a.stderr, b.stderr)
+        (tmp_path / "a.txt").write_text(a.stdout); (tmp_path / "b.txt").write_text(b.stdout)
+        ok, msg = cmp.equivalent(str(tmp_path / "a.txt"), str(tmp_path / "b.txt"))
+        assert ok, msg
+        assert a.stdout.startswith("U-CENTER: ") and b.stdout.count("\n") == 2
