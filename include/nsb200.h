@@ -63,7 +63,10 @@ enum {
     NSB_SOR_RESIDENT = 2, /* grid held in shared memory (one thread-block cluster, or one CTA per SM for grids
                              up to ~1024^2), all iterations in one launch; falls back to the stream engine */
     NSB_SOR_SIMPLE = 3,   /* one launch per colour + residual launch (validation kernel)        */
-    NSB_SOR_STREAM_LAUNCH = 4 /* the streaming pass with one launch per iteration on a single slab too */
+    NSB_SOR_STREAM_LAUNCH = 4, /* the streaming pass with one launch per iteration on a single slab too */
+    NSB_SOR_SERIAL_ORDER = 5   /* the SERIAL reference's order (integration.c:129-173): one ghost refresh per
+                                  iteration, in-place lexicographic sweep run as an anti-diagonal wavefront;
+                                  validation only (one CTA), single slab */
 };
 
 /* io.h:14 init(): the 15 positional values of a parameter file, same order */

@@ -30,7 +30,7 @@ U, V, P, F, G, RHS = 0, 1, 2, 3, 4, 5
 LAYOUT_REF, LAYOUT_XFAST = 0, 1
 NOT_CONVERGED = -1
 DIV_AUTO, DIV_EXACT, DIV_RECIP = 0, 1, 2
-SOR_AUTO, SOR_STREAM, SOR_RESIDENT, SOR_SIMPLE, SOR_STREAM_LAUNCH = 0, 1, 2, 3, 4
+SOR_AUTO, SOR_STREAM, SOR_RESIDENT, SOR_SIMPLE, SOR_STREAM_LAUNCH, SOR_SERIAL_ORDER = 0, 1, 2, 3, 4, 5
 
 dbl_p = C.POINTER(C.c_double)
 dbl_pp = C.POINTER(dbl_p)

@@ -192,6 +192,7 @@ cudaError_t nsb_launch_sor_begin(nsb_ctx* c);      // threshold from sum p^2, cl
 cudaError_t nsb_launch_sor_stream_iter(nsb_ctx* c, int it, const double* pin, double* pout, int check);
 int nsb_sor_persist_supported(const nsb_ctx* c);
 cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int n_iter, int check);   // all iterations, one launch
+cudaError_t nsb_launch_sor_lex(nsb_ctx* c, int max_it, int check);       // serial (lexicographic) order, validation
 cudaError_t nsb_launch_sor_simple_iter(nsb_ctx* c, int it, double* p, int check);
 cudaError_t nsb_launch_sor_finish_ghosts(nsb_ctx* c, double* pfinal, const double* pprev);
 cudaError_t nsb_launch_to_xfast(nsb_ctx* c, const double* src_ref, double* dst);   // [i][j] -> grid

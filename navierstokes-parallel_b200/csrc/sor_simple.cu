@@ -165,3 +165,80 @@ cudaError_t nsb_launch_sor_finish_ghosts(nsb_ctx* c, double* pfinal, const doubl
                                                                      c->wall_bottom ? 1 : 0, c->wall_top ? 1 : 0);
     return NSB_LAUNCHED(c, 1);
 }
+
+// ------------------------------------------------------------------------------------------
+// Serial-order engine (validation only): the reference's CPU solver sweeps the grid
+// lexicographically in place, i outer / j inner (src/serial/integration.c:149-154), refreshes the
+// ghost cells ONCE per iteration (138-146) and evaluates the residual with those same ghosts
+// (156-160).  Cell (i, j) then depends on the NEW values of (i-1, j) and (i, j-1) and the OLD values
+// of (i+1, j) and (i, j+1): all cells of one anti-diagonal i + j = d are independent, and sweeping
+// the diagonals in increasing d reproduces the lexicographic result bit for bit.  One CTA walks the
+// diagonals with a block barrier between them -- low throughput by construction; it
+// exists so that whole runs can be compared with the reference's SERIAL binary including its
+// iteration counts.  norm_p = sqrt(sum / i_max / j_max) as in L2() (integration.c:115-124).
+#define LEX_THREADS 1024
+
+template <bool RECIP>
+__global__ void __launch_bounds__(LEX_THREADS, 1) sor_lex_kernel(double* p, const double* __restrict__ rhs, long long pitch,
+                                                                  int ni, int nj, SorCoef k, double eps, const StepRed* red,
+                                                                  SorCtl* ctl, int max_it, int check) {
+    __shared__ double sh[32];
+    __shared__ double res_sh;
+    double* P = p + (long long)NSB_ROW0 * pitch + NSB_COL0;
+    const double* Q = rhs + (long long)NSB_ROW0 * pitch + NSB_COL0;
+    const int tid = threadIdx.x;
+    const double norm_p = sqrt(red->sum_p2 / (double)ni / (double)nj);
+    const double thresh = eps * (norm_p + 1.5);
+    int it = 0, converged = 0;
+    double res = 0.0, total = 0.0;
+    while (it < max_it) {
+        for (int j = 1 + tid; j <= nj; j += LEX_THREADS) {                    // integration.c:138-142
+            P[(long long)j * pitch] = P[(long long)j * pitch + 1];
+            P[(long long)j * pitch + ni + 1] = P[(long long)j * pitch + ni];
+        }
+        for (int i = 1 + tid; i <= ni; i += LEX_THREADS) {                    // integration.c:143-146
+            P[i] = P[pitch + i];
+            P[(long long)(nj + 1) * pitch + i] = P[(long long)nj * pitch + i];
+        }
+        __syncthreads();
+        for (int d = 2; d <= ni + nj; d++) {                                  // integration.c:149-154 as a wavefront
+            const int ilo = max(1, d - nj), ihi = min(ni, d - 1);
+            for (int i = ilo + tid; i <= ihi; i += LEX_THREADS) {
+                const long long o = (long long)(d - i) * pitch + i;
+                P[o] = sor_cell<RECIP>(P[o], P[o + 1], P[o - 1], P[o + pitch], P[o - pitch], Q[o], k);
+            }
+            __syncthreads();
+        }
+        double acc = 0.0;                                                     // integration.c:156-164
+        for (int j = 1 + (tid >> 5); j <= nj; j += LEX_THREADS / 32)
+            for (int i = 1 + (tid & 31); i <= ni; i += 32) {
+                const long long o = (long long)j * pitch + i;
+                const double r = sor_residual<RECIP>(P[o], P[o + 1], P[o - 1], P[o + pitch], P[o - pitch], Q[o], k);
+                acc = fma(r, r, acc);
+            }
+        const double t = block_sum(acc, sh);
+        if (tid == 0) { total = t; res_sh = sqrt(t / (double)ni / (double)nj); }
+        __syncthreads();
+        res = res_sh;
+        it++;
+        if (res <= thresh) { converged = 1; if (check) break; }               // integration.c:164-166
+        __syncthreads();
+    }
+    if (tid == 0) {
+        ctl->norm_p = norm_p; ctl->thresh = thresh;
+        if (it > 0) { ctl->res = res; ctl->sum_r2 = total; }
+        ctl->converged = converged;
+        __threadfence();
+        *((volatile int*)&ctl->iters) = it;
+        __threadfence();
+        sor_publish(ctl);
+    }
+}
+
+cudaError_t nsb_launch_sor_lex(nsb_ctx* c, int max_it, int check) {
+    const SorCoef k = make_coef(c);
+    double* p = c->pbuf[c->pcur];
+    if (c->use_recip) sor_lex_kernel<true><<<1, LEX_THREADS, 0, c->stream>>>(p, c->rhs, c->g.pitch, c->g.ni, c->g.nj, k, c->P.epsilon, c->d_red, c->d_ctl, max_it, check);
+    else sor_lex_kernel<false><<<1, LEX_THREADS, 0, c->stream>>>(p, c->rhs, c->g.pitch, c->g.ni, c->g.nj, k, c->P.epsilon, c->d_red, c->d_ctl, max_it, check);
+    return NSB_LAUNCHED(c, 1);
+}

@@ -155,6 +155,7 @@ static int pick_engine(const nsb_ctx* c) {
         if (e == NSB_SOR_STREAM_LAUNCH || !nsb_sor_persist_supported(c)) return NSB_SOR_STREAM_LAUNCH;
         return NSB_SOR_STREAM;
     }
+    if (e == NSB_SOR_SERIAL_ORDER) return e;
     if (e == NSB_SOR_AUTO) e = nsb_sor_resident_supported(c) ? NSB_SOR_RESIDENT : NSB_SOR_STREAM;
     if (e == NSB_SOR_RESIDENT && !nsb_sor_resident_supported(c)) e = NSB_SOR_STREAM;
     if (e == NSB_SOR_STREAM && !nsb_sor_persist_supported(c)) e = NSB_SOR_STREAM_LAUNCH;
@@ -178,6 +179,11 @@ static int sor_iterate(nsb_ctx** cs, int n, int max_it, int check) {
     if (engine == NSB_SOR_RESIDENT) {
         CU(c0, cudaSetDevice(c0->device));
         CU(c0, nsb_launch_sor_resident(c0, max_it, check));
+        return NSB_OK;
+    }
+    if (engine == NSB_SOR_SERIAL_ORDER) {
+        CU(c0, cudaSetDevice(c0->device));
+        CU(c0, nsb_launch_sor_lex(c0, max_it, check));
         return NSB_OK;
     }
     if (engine == NSB_SOR_STREAM) {                            // every iteration of the solve in one launch per rank
