@@ -153,8 +153,9 @@ def main():
     nj = size * world if (world > 1 and args.scaling == "weak") else size     # global rows
     cells = float(ni) * float(nj)                                             # global cells
     if world == 1:
+        which = {8192: "configs[2]", 16384: "configs[3] grid on one GPU", 32768: "configs[4] box on one GPU"}.get(size, "other size")
         workload = (f"synthetic lid-driven cavity {size}x{size} FP64, Re=1000, omega=1.7, eps=1e-4, "
-                    f"max_it={max_it} (BASELINE.json configs[2])")
+                    f"max_it={max_it} (BASELINE.json {which})")
         par = "single GPU"
     elif args.scaling == "weak":
         workload = (f"synthetic lid-driven cavity {ni}x{nj} FP64 ({size}^2 cells per GPU, box {1}x{world}), Re=1000, "
