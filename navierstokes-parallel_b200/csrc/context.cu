@@ -185,6 +185,10 @@ int nsb_create_slab_internal(const nsb_params* P, const nsb_options* opt, int ra
     // pitch: COL0 + (ni+2) columns + one spare group, rounded up to 16 doubles (128 B)
     long long need = NSB_COL0 + (long long)P->i_max + 2 + NSB_GROUP;
     c->g.pitch = (need + 15) / 16 * 16;
+    {   // tuning hook: extra padding of every row (doubles, rounded to 128 B)
+        const char* ex = getenv("NSB_PITCH_EXTRA");
+        if (ex && atoi(ex) > 0) c->g.pitch += (atoi(ex) + 15) / 16 * 16;
+    }
     c->g.rows = c->g.nj + 2 + NSB_ROW0 + NSB_ROWS_ABOVE;
     c->g.elems = (size_t)c->g.pitch * (size_t)c->g.rows;
 
