@@ -432,6 +432,8 @@ __device__ __forceinline__ double sor_run_task(TaskCtx& t, const SorCoef& kf, co
         const bool clean = (jb - 3 >= t.jc0) && (jb + 5 <= t.jc1) && (jb + 7 <= t.nj) &&
                            !(t.push_down && jb - 2 <= 3) && !(t.push_up && jb + 5 >= t.nj - 2);
 #endif
+        // (a fourth variant <EX, !EY> for the interior rows of the two edge strips was measured: the larger
+        //  kernel body costs the LEAN path 10 % -- 5.27 against 5.86 TB/s at 8192^2 -- and was dropped)
         if (EX) sor_block8<RECIP, true, true>(P, R, sb, t, kf, lg, acc);
         else if (clean) sor_block8<RECIP, false, false>(P, R, sb, t, kf, lg, acc);
         else sor_block8<RECIP, false, true>(P, R, sb, t, kf, lg, acc);
