@@ -131,6 +131,8 @@ struct nsb_ctx {
     bool own_stream;
     double dx, dy;
     bool recip_exact;      // dx2 and dy2 are powers of two -> reciprocal multiply is exact
+    bool rcp_valid;        // rcp_val = nsb_rcp_refined(rcp_key) (IEEE division path, nsb_make_sor_coef)
+    double rcp_key[2], rcp_val[2];
     bool use_recip;        // resolved division mode
     // grids
     double* u; double* v; double* F; double* G; double* rhs;
@@ -194,6 +196,7 @@ int nsb_sor_persist_supported(const nsb_ctx* c);
 cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int n_iter, int check);   // all iterations, one launch
 cudaError_t nsb_launch_sor_lex(nsb_ctx* c, int max_it, int check);       // serial (lexicographic) order, validation
 cudaError_t nsb_launch_sor_simple_iter(nsb_ctx* c, int it, double* p, int check);
+SorCoef nsb_make_sor_coef(nsb_ctx* c, long long cells);                  // sor_simple.cu; cells = GLOBAL i_max * j_max
 cudaError_t nsb_launch_sor_finish_ghosts(nsb_ctx* c, double* pfinal, const double* pprev);
 cudaError_t nsb_launch_to_xfast(nsb_ctx* c, const double* src_ref, double* dst);   // [i][j] -> grid
 cudaError_t nsb_launch_from_xfast(nsb_ctx* c, const double* src, double* dst_ref); // grid -> [i][j]

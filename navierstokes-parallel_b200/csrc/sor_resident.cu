@@ -384,11 +384,7 @@ cudaError_t nsb_launch_sor_resident(nsb_ctx* c, int max_it, int check) {
     memset(&a, 0, sizeof a);
     a.p = c->pbuf[c->pcur]; a.rhs = c->rhs; a.pitch = c->g.pitch; a.ni = c->g.ni; a.nj = c->g.nj;
     a.W = pl.W; a.rows_per_cta = pl.rows_per_cta; a.max_it = max_it; a.check = check; a.it0 = 0;
-    const double dx2 = c->dx * c->dx, dy2 = c->dy * c->dy;
-    a.k.om1 = 1.0 - c->P.omega;
-    a.k.w = c->P.omega / (2.0 * (1.0 / dx2 + 1.0 / dy2));
-    a.k.dx2 = dx2; a.k.dy2 = dy2; a.k.rdx2 = 1.0 / dx2; a.k.rdy2 = 1.0 / dy2;
-    a.k.cells = (long long)c->g.ni * (long long)c->J;
+    a.k = nsb_make_sor_coef(c, (long long)c->g.ni * (long long)c->J);
     a.ctl = c->d_ctl;
     cudaError_t e;
     if (pl.grid) {

@@ -104,14 +104,38 @@ __global__ void sor_residual_kernel(const double* __restrict__ p, const double* 
     }
 }
 
-static SorCoef make_coef(const nsb_ctx* c) {
+// ---- the scalars of a solve.  With IEEE division the kernels need nsb_rcp_refined(dx2 / dy2)
+// (nsb_math.cuh): a one-thread kernel computes them once per (dx, dy) and the values are cached.
+__device__ double g_rcp_out[2];
+__global__ void rcp_refine_kernel(double dx2, double dy2) {
+    g_rcp_out[0] = nsb_rcp_refined(dx2);
+    g_rcp_out[1] = nsb_rcp_refined(dy2);
+}
+
+SorCoef nsb_make_sor_coef(nsb_ctx* c, long long cells) {
     SorCoef k;
     const double dx2 = c->dx * c->dx, dy2 = c->dy * c->dy;
     k.om1 = 1.0 - c->P.omega;
     k.w = c->P.omega / (2.0 * (1.0 / dx2 + 1.0 / dy2));
     k.dx2 = dx2; k.dy2 = dy2; k.rdx2 = 1.0 / dx2; k.rdy2 = 1.0 / dy2;
     k.inv_cells_unused = 0.0;
-    k.cells = (long long)c->g.ni * (long long)c->g.nj;
+    k.cells = cells;
+    if (!c->use_recip) {
+        if (!c->rcp_valid || c->rcp_key[0] != dx2 || c->rcp_key[1] != dy2) {
+            rcp_refine_kernel<<<1, 1, 0, c->stream>>>(dx2, dy2);
+            double out[2] = {0.0, 0.0};
+            cudaError_t e = cudaMemcpyFromSymbolAsync(out, g_rcp_out, sizeof out, 0, cudaMemcpyDeviceToHost, c->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+            // a failed refinement leaves the plain reciprocal: nsb_div_const then still returns the
+            // IEEE quotient whenever its three steps do (the error surfaces at the next launch)
+            if (e == cudaSuccess && out[0] != 0.0 && out[1] != 0.0) {
+                c->rcp_key[0] = dx2; c->rcp_key[1] = dy2;
+                c->rcp_val[0] = out[0]; c->rcp_val[1] = out[1];
+                c->rcp_valid = true;
+            }
+        }
+        if (c->rcp_valid) { k.rdx2 = c->rcp_val[0]; k.rdy2 = c->rcp_val[1]; }
+    }
     return k;
 }
 
@@ -120,7 +144,7 @@ static SorCoef make_coef(const nsb_ctx* c) {
 cudaError_t nsb_launch_sor_simple_iter(nsb_ctx* c, int it, double* p, int check) {
     const SorCtl* ck = check ? c->d_ctl : nullptr;
     const int ni = c->g.ni, nj = c->g.nj;
-    const SorCoef k = make_coef(c);
+    const SorCoef k = nsb_make_sor_coef(c, (long long)c->g.ni * (long long)c->g.nj);
     const int nb = (max(ni, nj) + 255) / 256;
     const int half = (ni + 1) / 2;
     dim3 cgrid((half + 127) / 128, nj);
@@ -236,9 +260,88 @@ __global__ void __launch_bounds__(LEX_THREADS, 1) sor_lex_kernel(double* p, cons
 }
 
 cudaError_t nsb_launch_sor_lex(nsb_ctx* c, int max_it, int check) {
-    const SorCoef k = make_coef(c);
+    const SorCoef k = nsb_make_sor_coef(c, (long long)c->g.ni * (long long)c->g.nj);
     double* p = c->pbuf[c->pcur];
     if (c->use_recip) sor_lex_kernel<true><<<1, LEX_THREADS, 0, c->stream>>>(p, c->rhs, c->g.pitch, c->g.ni, c->g.nj, k, c->P.epsilon, c->d_red, c->d_ctl, max_it, check);
     else sor_lex_kernel<false><<<1, LEX_THREADS, 0, c->stream>>>(p, c->rhs, c->g.pitch, c->g.ni, c->g.nj, k, c->P.epsilon, c->d_red, c->d_ctl, max_it, check);
     return NSB_LAUNCHED(c, 1);
+}
+
+// ------------------------------------------------------------------------------------------
+// Self-check of nsb_div_try / nsb_div_full against __ddiv_rn (development / test aid, not in the header):
+// n quotients x / d per mode, x from a counter-based generator.  mode 0: random significand,
+// exponent in [-64, 64] (field data); 1: random 64-bit patterns (all exponents, NaN, Inf,
+// denormals); 2: zeros, denormals and the edges of the exponent window.  NaN == NaN here.
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
+    z += 0x9e3779b97f4a7c15ull;
+    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+    z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+    return z ^ (z >> 31);
+}
+__global__ void divcheck_kernel(double d1, double d2, double r1, double r2, long long n, unsigned long long seed, int mode,
+                                unsigned long long* bad, double* first_bad) {
+    unsigned long long local = 0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const unsigned long long h = mix64(seed + 2ull * (unsigned long long)i), h2 = mix64(h);
+        double x1, x2;
+        if (mode == 0) {
+            const long long e1 = 1023 - 64 + (long long)((h >> 52) % 129ull), e2 = 1023 - 64 + (long long)((h2 >> 52) % 129ull);
+            x1 = __longlong_as_double((long long)((h & 0x800fffffffffffffull) | ((unsigned long long)e1 << 52)));
+            x2 = __longlong_as_double((long long)((h2 & 0x800fffffffffffffull) | ((unsigned long long)e2 << 52)));
+        } else if (mode == 1) {
+            x1 = __longlong_as_double((long long)h); x2 = __longlong_as_double((long long)h2);
+        } else {
+            const unsigned long long sel = h >> 61;
+            const unsigned long long m = h2 & 0x000fffffffffffffull;
+            const unsigned long long sgn = h & 0x8000000000000000ull >> 0;
+            unsigned long long b;
+            if (sel == 0) b = 0ull;                                        // +-0
+            else if (sel == 1) b = m;                                      // denormal
+            else if (sel == 2) b = (0x035ull << 52) | m;                   // just below the window
+            else if (sel == 3) b = (0x036ull << 52) | m;                   // lower edge
+            else if (sel == 4) b = (0x7f7ull << 52) | m;                   // upper edge
+            else if (sel == 5) b = (0x7feull << 52) | m;                   // largest finite
+            else if (sel == 6) b = (0x001ull << 52) | m;                   // smallest normal
+            else b = (0x7ffull << 52) | (m & 1ull ? m : 0ull);             // Inf / NaN
+            x1 = __longlong_as_double((long long)(b | (sgn & 0x8000000000000000ull)));
+            x2 = -x1;
+        }
+        // inside the window (w1 / w2 stay true) the three-operation quotient must BE the division;
+        // outside, the callers fall back to nsb_div_full
+        bool w1 = true, w2 = true;
+        double q1 = nsb_div_try(x1, d1, r1, w1), q2 = nsb_div_try(x2, d2, r2, w2);
+        if (!w1) q1 = nsb_div_full(x1, d1);
+        if (!w2) q2 = nsb_div_full(x2, d2);
+        const double t1 = __ddiv_rn(x1, d1), t2 = __ddiv_rn(x2, d2);
+        const bool ok1 = (__double_as_longlong(q1) == __double_as_longlong(t1)) || (q1 != q1 && t1 != t1);
+        const bool ok2 = (__double_as_longlong(q2) == __double_as_longlong(t2)) || (q2 != q2 && t2 != t2);
+        if (mode == 0 && !(w1 && w2)) atomicAdd(bad + 1, 1ull << 32);   // field-like operands must never leave the window
+        if (!ok1 || !ok2) {
+            local++;
+            if ((atomicAdd(bad + 1, 1ull) & 0xffffffffull) == 0ull) { first_bad[0] = ok1 ? x2 : x1; first_bad[1] = ok1 ? d2 : d1; }
+        }
+    }
+    if (local) atomicAdd(bad, local);
+}
+
+extern "C" int nsb_debug_divcheck(double d1, double d2, long long n, unsigned long long seed, int mode,
+                                  long long* mismatches, double* first_bad_x, double* first_bad_d) {
+    unsigned long long* bad = nullptr;
+    double* fb = nullptr;
+    if (cudaMalloc(&bad, 16) != cudaSuccess || cudaMalloc(&fb, 16) != cudaSuccess) return NSB_ERR_CUDA;
+    cudaMemset(bad, 0, 16); cudaMemset(fb, 0, 16);
+    rcp_refine_kernel<<<1, 1>>>(d1, d2);
+    double r[2] = {0.0, 0.0};
+    cudaMemcpyFromSymbol(r, g_rcp_out, sizeof r);
+    divcheck_kernel<<<148 * 8, 256>>>(d1, d2, r[0], r[1], n, seed, mode, bad, fb);
+    unsigned long long hb[2] = {0, 0};
+    double hf[2] = {0.0, 0.0};
+    cudaError_t e = cudaMemcpy(hb, bad, 16, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(hf, fb, 16, cudaMemcpyDeviceToHost);
+    cudaFree(bad); cudaFree(fb);
+    if (e != cudaSuccess) return NSB_ERR_CUDA;
+    if (mismatches) *mismatches = (long long)hb[0] + (long long)(hb[1] >> 32);   // + field-like operands outside the window
+    if (first_bad_x) *first_bad_x = hf[0];
+    if (first_bad_d) *first_bad_d = hf[1];
+    return NSB_OK;
 }

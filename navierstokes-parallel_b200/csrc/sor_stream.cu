@@ -235,9 +235,12 @@ __device__ __forceinline__ void issue_pair(TaskCtx& t, int st, uint32_t empty_ph
 // this step is j = jstart + sb + S.
 //   EX: the strip holds ghost / pad columns (first and last strips).
 //   EY: the block of 8 steps touches rows that need gating (walls, chunk ends).
-template <bool RECIP, bool EX, bool EY, int S>
+//   QM: how quotients are formed (nsb_math.cuh); with NSB_QUOT_TRY `ok` is cleared when a quotient that
+//       is USED left the window of the three-operation division (pad / ghost columns of an edge strip may
+//       hold anything and are not counted).
+template <int QM, bool EX, bool EY, int S>
 __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], const int sb, TaskCtx& t,
-                                         const SorCoef& kf, const LaneGeom& lg, double& acc) {
+                                         const SorCoef& kf, const LaneGeom& lg, double& acc, bool& ok) {
     constexpr int sE = S & 7, sD = (S + 7) & 7, sC = (S + 6) & 7, sB = (S + 5) & 7, sA = (S + 4) & 7;
     constexpr int st = (S >> 1) & (SOR_NST - 1);
     constexpr int k0 = (S & 1) ? 1 : 0;     // cells updated this step: columns k0 and k0 + 2
@@ -300,10 +303,11 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
         const double e0 = X[k0 + 1];
         const double w1 = X[k1 - 1];
         const double e1 = (k1 == 3) ? xe : X[(k1 + 1) & 3];
-        const double u0 = sor_cell<RECIP>(X[k0], e0, w0, P[sE][k0], P[sC][k0], R[sD][k0], kf);
-        const double u1 = sor_cell<RECIP>(X[k1], e1, w1, P[sE][k1], P[sC][k1], R[sD][k1], kf);
-        if (row_in && (!EX || lg.inner[k0])) X[k0] = u0;
-        if (row_in && (!EX || lg.inner[k1])) X[k1] = u1;
+        bool ok0 = true, ok1 = true;
+        const double u0 = sor_cell_q<QM>(X[k0], e0, w0, P[sE][k0], P[sC][k0], R[sD][k0], kf, EX ? ok0 : ok);
+        const double u1 = sor_cell_q<QM>(X[k1], e1, w1, P[sE][k1], P[sC][k1], R[sD][k1], kf, EX ? ok1 : ok);
+        if (row_in && (!EX || lg.inner[k0])) { X[k0] = u0; if (EX) ok = ok && ok0; }
+        if (row_in && (!EX || lg.inner[k1])) { X[k1] = u1; if (EX) ok = ok && ok1; }
     }
 
     // ---- colour 1 (black) on row C = j-2; neighbours B (j-3, final) and D (j-1, red done)
@@ -329,10 +333,11 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
         const double e0 = X[k0 + 1];
         const double w1 = X[k1 - 1];
         const double e1 = (k1 == 3) ? xe : X[(k1 + 1) & 3];
-        const double u0 = sor_cell<RECIP>(X[k0], e0, w0, P[sD][k0], P[sB][k0], R[sC][k0], kf);
-        const double u1 = sor_cell<RECIP>(X[k1], e1, w1, P[sD][k1], P[sB][k1], R[sC][k1], kf);
-        if (row_in && (!EX || lg.inner[k0])) X[k0] = u0;
-        if (row_in && (!EX || lg.inner[k1])) X[k1] = u1;
+        bool ok0 = true, ok1 = true;
+        const double u0 = sor_cell_q<QM>(X[k0], e0, w0, P[sD][k0], P[sB][k0], R[sC][k0], kf, EX ? ok0 : ok);
+        const double u1 = sor_cell_q<QM>(X[k1], e1, w1, P[sD][k1], P[sB][k1], R[sC][k1], kf, EX ? ok1 : ok);
+        if (row_in && (!EX || lg.inner[k0])) { X[k0] = u0; if (EX) ok = ok && ok0; }
+        if (row_in && (!EX || lg.inner[k1])) { X[k1] = u1; if (EX) ok = ok && ok1; }
         if (EX && (!EY || (r >= t.jc0 && r <= t.jc1))) {
             // ghost columns of the final row, as the refresh before colour 1 left them (main.cu:694):
             // the west ghost lives in the halo lane 0 of the first strip, the east ghost in an owner
@@ -392,30 +397,31 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
             for (int k = 0; k < 4; k++) {
                 const double w = (k == 0) ? xw : X[(k + 3) & 3];
                 const double e = (k == 3) ? xe : X[(k + 1) & 3];
-                const double q = sor_residual<RECIP>(X[k], e, w, P[sC][k], P[sA][k], R[sB][k], kf);
-                if (!EX || lg.inner[k]) part = fma(q, q, part);
+                bool okr = true;
+                const double q = sor_residual_q<QM>(X[k], e, w, P[sC][k], P[sA][k], R[sB][k], kf, EX ? okr : ok);
+                if (!EX || lg.inner[k]) { part = fma(q, q, part); if (EX) ok = ok && okr; }
             }
             acc += part;                           // non-owner lanes are discarded at the end of the task
         }
     }
 }
 
-template <bool RECIP, bool EX, bool EY>
+template <int QM, bool EX, bool EY>
 __device__ __forceinline__ void sor_block8(double (&P)[8][4], double (&R)[8][4], const int sb, TaskCtx& t,
-                                           const SorCoef& kf, const LaneGeom& lg, double& acc) {
-    sor_step<RECIP, EX, EY, 0>(P, R, sb, t, kf, lg, acc);
-    sor_step<RECIP, EX, EY, 1>(P, R, sb, t, kf, lg, acc);
-    sor_step<RECIP, EX, EY, 2>(P, R, sb, t, kf, lg, acc);
-    sor_step<RECIP, EX, EY, 3>(P, R, sb, t, kf, lg, acc);
-    sor_step<RECIP, EX, EY, 4>(P, R, sb, t, kf, lg, acc);
-    sor_step<RECIP, EX, EY, 5>(P, R, sb, t, kf, lg, acc);
-    sor_step<RECIP, EX, EY, 6>(P, R, sb, t, kf, lg, acc);
-    sor_step<RECIP, EX, EY, 7>(P, R, sb, t, kf, lg, acc);
+                                           const SorCoef& kf, const LaneGeom& lg, double& acc, bool& ok) {
+    sor_step<QM, EX, EY, 0>(P, R, sb, t, kf, lg, acc, ok);
+    sor_step<QM, EX, EY, 1>(P, R, sb, t, kf, lg, acc, ok);
+    sor_step<QM, EX, EY, 2>(P, R, sb, t, kf, lg, acc, ok);
+    sor_step<QM, EX, EY, 3>(P, R, sb, t, kf, lg, acc, ok);
+    sor_step<QM, EX, EY, 4>(P, R, sb, t, kf, lg, acc, ok);
+    sor_step<QM, EX, EY, 5>(P, R, sb, t, kf, lg, acc, ok);
+    sor_step<QM, EX, EY, 6>(P, R, sb, t, kf, lg, acc, ok);
+    sor_step<QM, EX, EY, 7>(P, R, sb, t, kf, lg, acc, ok);
 }
 
 // One task = one strip x one chunk of rows, marched bottom to top by one warp.
-template <bool RECIP, bool EX>
-__device__ __forceinline__ double sor_run_task(TaskCtx& t, const SorCoef& kf, const LaneGeom& lg) {
+template <int QM, bool EX>
+__device__ __forceinline__ double sor_run_task(TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, bool& ok) {
     double P[8][4], R[8][4];
 #pragma unroll
     for (int s = 0; s < 8; s++)
@@ -434,11 +440,53 @@ __device__ __forceinline__ double sor_run_task(TaskCtx& t, const SorCoef& kf, co
 #endif
         // (a fourth variant <EX, !EY> for the interior rows of the two edge strips was measured: the larger
         //  kernel body costs the LEAN path 10 % -- 5.27 against 5.86 TB/s at 8192^2 -- and was dropped)
-        if (EX) sor_block8<RECIP, true, true>(P, R, sb, t, kf, lg, acc);
-        else if (clean) sor_block8<RECIP, false, false>(P, R, sb, t, kf, lg, acc);
-        else sor_block8<RECIP, false, true>(P, R, sb, t, kf, lg, acc);
+        if (EX) sor_block8<QM, true, true>(P, R, sb, t, kf, lg, acc, ok);
+        else if (clean && QM != NSB_QUOT_FULL) sor_block8<QM, false, false>(P, R, sb, t, kf, lg, acc, ok);
+        else sor_block8<QM, false, true>(P, R, sb, t, kf, lg, acc, ok);
     }
     return lg.owner ? acc : 0.0;
+}
+
+// Phase parities of a warp's mbarriers after one task of n_steps rows (see sor_persist_kernel).
+__device__ __forceinline__ void sor_advance_parities(int n_steps, uint32_t& full_par, uint32_t& empty_par) {
+    const uint32_t pairs_per_stage = (uint32_t)(((n_steps + 7) / 8) * 4 / SOR_NST);
+    full_par ^= (pairs_per_stage + 1u) & 1u;
+    empty_par ^= pairs_per_stage & 1u;
+}
+
+// A whole task: the first row pairs are requested, the strip is marched.  With the IEEE division the
+// first pass uses the three-operation quotients; if any lane saw an operand outside their window
+// (non-finite or denormal-range data) the SAME task runs again with out-of-line divisions -- its
+// outputs (rows, halo rows, partial) are simply written twice, nothing is published in between.
+// `row0` = &array[row jstart][first column of the strip] offsets, as set up by the caller.
+template <bool RECIP>
+__device__ __forceinline__ double sor_task(TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, bool edge_strip,
+                                           uint32_t& full_par, uint32_t& empty_par) {
+    constexpr int QM = RECIP ? NSB_QUOT_RECIP : NSB_QUOT_TRY;
+    const int n_steps = t.jc1 + 3 - t.jstart + 1;
+    const double* pin0 = t.pin_next; const double* rhs0 = t.rhs_next; double* pout0 = t.pout_row;
+    t.full_par = full_par; t.empty_par = empty_par;
+    sor_advance_parities(n_steps, full_par, empty_par);
+    __syncwarp();
+#pragma unroll
+    for (int q = 0; q < SOR_NST; q++) issue_pair(t, q, 0u, false);
+    bool ok = true;
+    double acc;
+    if (edge_strip) acc = sor_run_task<QM, true>(t, kf, lg, ok);
+    else acc = sor_run_task<QM, false>(t, kf, lg, ok);
+    if (!RECIP) {
+        if (!__all_sync(0xffffffffu, ok)) {
+            t.pin_next = pin0; t.rhs_next = rhs0; t.pout_row = pout0; t.j_next = t.jstart;
+            t.full_par = full_par; t.empty_par = empty_par;
+            sor_advance_parities(n_steps, full_par, empty_par);
+            __syncwarp();
+#pragma unroll
+            for (int q = 0; q < SOR_NST; q++) issue_pair(t, q, 0u, false);
+            if (edge_strip) acc = sor_run_task<NSB_QUOT_FULL, true>(t, kf, lg, ok);
+            else acc = sor_run_task<NSB_QUOT_FULL, false>(t, kf, lg, ok);
+        }
+    }
+    return acc;
 }
 
 #ifdef SOR_MAXNREG
@@ -539,13 +587,8 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         }
-        __syncwarp();
-#pragma unroll
-        for (int s = 0; s < SOR_NST; s++) issue_pair(t, s, 0u, false);
-
-        double acc;
-        if (edge_strip) acc = sor_run_task<RECIP, true>(t, a.k, lg);
-        else acc = sor_run_task<RECIP, false>(t, a.k, lg);
+        uint32_t full_par = 0u, empty_par = 0u;
+        double acc = sor_task<RECIP>(t, a.k, lg, edge_strip, full_par, empty_par);
         acc = warp_sum(acc);
         if (lane == 0) a.partials[chunk * a.n_strips + strip] = acc;
 
@@ -780,20 +823,7 @@ __global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
             asm volatile("fence.proxy.async;" ::: "memory");
         }
 
-        t.full_par = full_par; t.empty_par = empty_par;
-        {
-            const int n_steps = t.jc1 + 3 - t.jstart + 1;
-            const uint32_t pairs_per_stage = (uint32_t)(((n_steps + 7) / 8) * 4 / SOR_NST);
-            full_par ^= (pairs_per_stage + 1u) & 1u;
-            empty_par ^= pairs_per_stage & 1u;
-        }
-        __syncwarp();
-#pragma unroll
-        for (int q = 0; q < SOR_NST; q++) issue_pair(t, q, 0u, false);
-
-        double acc;
-        if (edge_strip) acc = sor_run_task<RECIP, true>(t, a.k, lg);
-        else acc = sor_run_task<RECIP, false>(t, a.k, lg);
+        double acc = sor_task<RECIP>(t, a.k, lg, edge_strip, full_par, empty_par);
         acc = warp_sum(acc);
         double* part = pa.partials2 + (size_t)(it & 1) * a.n_tasks;
         if (lane == 0) part[tslot] = acc;
@@ -900,11 +930,17 @@ void nsb_sor_plan(nsb_ctx* c) {
     double best_cost = 1e300;
     if (c->O.sor_chunk_rows > 0) {
         best = (c->O.sor_chunk_rows + 1) & ~1;
-    } else if ((long long)((nj + 119) / 120) * c->n_strips >= 2 * slots) {
-        // Large grids: 120-row chunks, several waves of blocks.  The hardware block scheduler then
-        // balances the load (one 241-row wave at 8192^2 left the average SM idle for 20 % of the
-        // launch; measured 363 us against 320 us, profiles/r1c_chunk_sweep.txt).
-        best = 120;
+    } else if ((long long)((nj + 119) / 120) * c->n_strips >= slots) {
+        // Large grids: about two tasks per resident warp and iteration, chunks of 64 .. 120 rows
+        // (3 + 3 halo rows are read twice, so not lower).  The persistent sweep overlaps the tail
+        // of one iteration with the head of the next, but only with enough tasks to hand out:
+        // 6144^2 with one 184-row task per warp 217 us per iteration, with 96-row tasks 170 us;
+        // 5120^2 161 -> 143 us (profiles/r1h_chunk_sweep.txt).  8192^2 keeps 120 rows (one
+        // 241-row wave left the average SM idle for 20 % of a launch, profiles/r1c_chunk_sweep.txt).
+        const long long want_chunks = (2 * slots + c->n_strips - 1) / c->n_strips;
+        int rows = (int)((nj + want_chunks - 1) / want_chunks);
+        rows = (rows + 1) & ~1;
+        best = rows < 64 ? 64 : rows > 120 ? 120 : rows;
     } else {
         for (int rows = 16; rows <= 2048; rows += 2) {
             long long chunks = (nj + rows - 1) / rows;
@@ -939,12 +975,7 @@ cudaError_t nsb_launch_sor_stream_iter(nsb_ctx* c, int it, const double* pin, do
     a.chunk_rows = c->chunk_rows; a.n_strips = c->n_strips; a.n_tasks = c->n_partials; a.n_chunks = c->n_chunks;
     a.n_groups = (int)(c->g.pitch / NSB_GROUP);
     a.it = it; a.check = check; a.zero = 0u;
-    const double dx2 = c->dx * c->dx, dy2 = c->dy * c->dy;
-    a.k.om1 = 1.0 - c->P.omega;
-    a.k.w = c->P.omega / (2.0 * (1.0 / dx2 + 1.0 / dy2));
-    a.k.dx2 = dx2; a.k.dy2 = dy2; a.k.rdx2 = 1.0 / dx2; a.k.rdy2 = 1.0 / dy2;
-    a.k.inv_cells_unused = 0.0;
-    a.k.cells = (long long)c->g.ni * (long long)c->J;          // main.cu:588: the GLOBAL cell count
+    a.k = nsb_make_sor_coef(c, (long long)c->g.ni * (long long)c->J);     // main.cu:588: the GLOBAL cell count
     a.partials = c->d_partials; a.bandvals = c->d_bandvals; a.ctl = c->d_ctl;
     a.world = c->world; a.wall_bottom = c->wall_bottom; a.wall_top = c->wall_top;
     a.seq = c->seq + (unsigned long long)it;
@@ -985,12 +1016,7 @@ cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int n_iter, int check) {
     a.chunk_rows = c->chunk_rows; a.n_strips = c->n_strips; a.n_tasks = c->n_partials; a.n_chunks = c->n_chunks;
     a.n_groups = (int)(c->g.pitch / NSB_GROUP);
     a.it = 0; a.check = check; a.zero = 0u;
-    const double dx2 = c->dx * c->dx, dy2 = c->dy * c->dy;
-    a.k.om1 = 1.0 - c->P.omega;
-    a.k.w = c->P.omega / (2.0 * (1.0 / dx2 + 1.0 / dy2));
-    a.k.dx2 = dx2; a.k.dy2 = dy2; a.k.rdx2 = 1.0 / dx2; a.k.rdy2 = 1.0 / dy2;
-    a.k.inv_cells_unused = 0.0;
-    a.k.cells = (long long)c->g.ni * (long long)c->J;
+    a.k = nsb_make_sor_coef(c, (long long)c->g.ni * (long long)c->J);     // main.cu:588: the GLOBAL cell count
     a.partials = c->d_partials; a.bandvals = c->d_bandvals; a.ctl = c->d_ctl;
     a.world = c->world; a.wall_bottom = c->wall_bottom; a.wall_top = c->wall_top;
     a.err = &c->d_sync->error;

@@ -165,6 +165,40 @@ def test_resident_grid_variant(ni, nj, monkeypatch):
     assert np.array_equal(got[0, 1:-1], want[0, 1:-1]) and np.array_equal(got[1:-1, 0], want[1:-1, 0])
 
 
+@pytest.mark.parametrize("engine", ["stream", "launch", "simple", "resident"])
+@pytest.mark.parametrize("ni,nj", [(150, 40), (400, 36)])
+def test_sor_outside_division_window(engine, ni, nj):
+    """IEEE division by dx^2 / dy^2 is done with a refined reciprocal and a residual correction that is
+    only valid inside an exponent window (nsb_math.cuh); operands outside it -- denormals, values next
+    to overflow -- and exact zeros of either sign must still give the reference's bits (the streaming
+    sweep repeats the task with real divisions, the other engines branch per cell)."""
+    m = nsb()
+    eng = dict(stream=m.SOR_STREAM, launch=m.SOR_STREAM_LAUNCH, simple=m.SOR_SIMPLE, resident=m.SOR_RESIDENT)[engine]
+    a, b = 1.0, 0.9
+    s, P = _solver(m, engine=eng, chunk_rows=16, i_max=ni, j_max=nj, a=a, b=b, omega=1.7)
+    p = _rand(s.shape, 31) * 0.5
+    rhs = _rand(s.shape, 32) * 3.0
+    # reference layout: [i][j].  A block of exact zeros (+0 and -0) with denormals inside, a block of huge values.
+    p[20:60, 5:30] = 0.0; p[30:40, 10:20] = -0.0; rhs[18:62, 3:32] = 0.0
+    p[25, 12] = 1e-310; p[45, 20] = -3e-320; p[50, 8] = 4.9e-324
+    big = 4e306 * (a / ni) ** 2          # quotients by dx^2 land between 2^1017 and overflow
+    p[100:110, 10:20] *= big
+    if ni > 300:
+        p[200:240, 4:34] = 0.0; rhs[198:242, 2:36] = 0.0; p[220, 20] = 1e-312; p[300:305, 6:12] *= big
+    s.upload(m.P, p); s.upload(m.RHS, rhs)
+    dx, dy = a / ni, b / nj
+    L = ob.lib()
+    with np.errstate(all="ignore"):
+        for n in (1, 2):
+            s.sor_iterations(n)
+            for _ in range(n):
+                L.orc_SOR_rb_iter(ob._ptr(p), ni, nj, dx, dy, ob._ptr(rhs), P.omega)
+            got = s.download(m.P)
+            assert np.all(np.isfinite(p[1:-1, 1:-1]))
+            assert np.array_equal(got[1:-1, 1:-1].view(np.int64), p[1:-1, 1:-1].view(np.int64))   # the sign of zero counts
+    s.close()
+
+
 @pytest.mark.parametrize("div_mode", ["exact", "recip"])
 def test_sor_division_modes(div_mode):
     """Non power-of-two spacing: NSB_DIV_EXACT (and AUTO) is bit-exact; NSB_DIV_RECIP stays within
@@ -533,3 +567,21 @@ def test_whole_run_matches_committed_serial_fixtures():
     assert runs
     for c in runs:
         _compare_run(m, c, m.SOR_SERIAL_ORDER)
+
+
+# ------------------------------------------------------------------------------- IEEE division by dx^2, dy^2
+@pytest.mark.parametrize("n", [130, 200, 1000, 1536, 3000, 6144, 10000])
+def test_division_by_constant_matches_ddiv(n):
+    """The sweep's x / dx^2 (refined reciprocal + residual correction, nsb_math.cuh) against __ddiv_rn, bit for bit:
+    2^27 pairs of field-like operands, 2^26 pairs of random bit patterns and 2^22 edge patterns (zeros, denormals,
+    the edges of the exponent window, Inf / NaN) per divisor pair."""
+    L = nsb().lib()
+    f = L.nsb_debug_divcheck
+    f.restype = C.c_int
+    f.argtypes = [C.c_double, C.c_double, C.c_longlong, C.c_ulonglong, C.c_int, C.POINTER(C.c_longlong),
+                  C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    dx, dy = 1.0 / n, 0.75 / (n + 7)
+    for mode, count in ((0, 1 << 27), (1, 1 << 26), (2, 1 << 22)):
+        bad, fx, fd = C.c_longlong(-1), C.c_double(), C.c_double()
+        assert f(dx * dx, dy * dy, count, 1234567 + n, mode, C.byref(bad), C.byref(fx), C.byref(fd)) == 0
+        assert bad.value == 0, f"mode {mode}: {bad.value} quotients differ, first x = {fx.value.hex()} d = {fd.value.hex()}"
