@@ -849,9 +849,27 @@ __global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
             // this warp closes iteration `it`: band sums in the fixed order of the per-iteration kernel
             __threadfence();
             if (lane == 0) pa.claim[1 + (it & 3)] = 0ull;
-            for (int b = 0; b < a.n_chunks; b++) {
-                const double v = warp_ordered_sum(part + (size_t)b * a.n_strips, a.n_strips, lane);
-                if (lane == 0) a.bandvals[b] = v;
+            // 16 bands at a time, so that 16 loads per lane are in flight: one band after the other
+            // (an L2 round trip each) took ~0.5 us per band, 40 us for the 86 bands of 2048^2 -- as long as
+            // the iteration itself, and iteration n+2 waits for this closing (ncu source page, 2048^2:
+            // half of all warp samples sat in the `iters` poll above).  Per band the additions are those
+            // of warp_ordered_sum (lane-strided partials in q order, then the butterfly): same bits.
+            for (int b0 = 0; b0 < a.n_chunks; b0 += 16) {
+                double sb[16];
+#pragma unroll
+                for (int u = 0; u < 16; u++) sb[u] = 0.0;
+                for (int q = lane; q < a.n_strips; q += 32) {
+#pragma unroll
+                    for (int u = 0; u < 16; u++)
+                        if (b0 + u < a.n_chunks) sb[u] += __ldcg(part + (size_t)(b0 + u) * a.n_strips + q);
+                }
+#pragma unroll
+                for (int u = 0; u < 16; u++) sb[u] = warp_sum(sb[u]);
+                if (lane == 0) {
+#pragma unroll
+                    for (int u = 0; u < 16; u++)
+                        if (b0 + u < a.n_chunks) a.bandvals[b0 + u] = sb[u];
+                }
             }
             __threadfence();
             __syncwarp();
@@ -930,23 +948,24 @@ void nsb_sor_plan(nsb_ctx* c) {
     double best_cost = 1e300;
     if (c->O.sor_chunk_rows > 0) {
         best = (c->O.sor_chunk_rows + 1) & ~1;
-    } else if ((long long)((nj + 119) / 120) * c->n_strips >= slots) {
-        // Large grids: about two tasks per resident warp and iteration, chunks of 64 .. 120 rows
-        // (3 + 3 halo rows are read twice, so not lower).  The persistent sweep overlaps the tail
-        // of one iteration with the head of the next, but only with enough tasks to hand out:
-        // 6144^2 with one 184-row task per warp 217 us per iteration, with 96-row tasks 170 us;
-        // 5120^2 161 -> 143 us (profiles/r1h_chunk_sweep.txt).  8192^2 keeps 120 rows (one
-        // 241-row wave left the average SM idle for 20 % of a launch, profiles/r1c_chunk_sweep.txt).
-        const long long want_chunks = (2 * slots + c->n_strips - 1) / c->n_strips;
-        int rows = (int)((nj + want_chunks - 1) / want_chunks);
-        rows = (rows + 1) & ~1;
-        best = rows < 64 ? 64 : rows > 120 ? 120 : rows;
     } else {
-        for (int rows = 16; rows <= 2048; rows += 2) {
-            long long chunks = (nj + rows - 1) / rows;
-            long long tasks = chunks * c->n_strips;
-            long long waves = (tasks + slots - 1) / slots;
-            double cost = (double)waves * (rows + 6 + 8);      // +8: pipeline fill / drain
+        // Chunk height of the persistent sweep, 16 .. 128 rows: minimise
+        //     max(tasks per resident warp and iteration, floor) x (rows + 18),   floor = 1.6
+        // -- a task costs its rows plus ~18 row-steps of overhead (3 + 3 halo rows, 8 steps of pipeline
+        // fill, claim / flag waits), and below ~1.6 tasks per warp there is nothing to overlap the
+        // dependency waits between two iterations with (4096^2: 50 chunks of 82 rows = one task per warp
+        // 110 us per iteration, 86 chunks of 48 rows 90 us).  Above 128 rows the tail of a launch and the
+        // balance between SMs suffer (8192^2: 240 rows 298 us, 128 rows 265 us).  Measured optima
+        // (profiles/r1h_chunk_sweep2.txt): 2048^2 16-24, 3072^2 32, 4096^2 48, 5120^2 48-80, 6144^2 64-112,
+        // 7168^2 96-104, 8192^2 120-128; the model picks 16, 28, 50, 78, 112, 128, 128.
+        // With the IEEE division the sweep is instruction bound instead of HBM bound and the balance between
+        // warps counts for more: the measured optima sit at ~2.7 tasks per warp (4096^2 32-48 rows, 5120^2 48,
+        // 6144^2 64-80, 7168^2 90, 8191^2 112; profiles/r1h_chunk_sweep2.txt), hence the higher floor.
+        const double floor_tasks = c->use_recip ? 1.6 : 2.6;
+        for (int rows = 16; rows <= 128; rows += 2) {
+            const long long chunks = (nj + rows - 1) / rows;
+            const double per_warp = (double)(chunks * c->n_strips) / (double)slots;
+            const double cost = (per_warp > floor_tasks ? per_warp : floor_tasks) * (rows + 18);
             if (cost < best_cost - 1e-9) { best_cost = cost; best = rows; }
             if (rows >= nj) break;
         }
