@@ -13,6 +13,7 @@
 #pragma once
 
 #include <cuda_runtime.h>
+#include <stddef.h>
 #include <stdint.h>
 
 #include "../../include/nsb200.h"
@@ -47,12 +48,14 @@ struct SorCtl {
     double norm_p;
     double res;          // residual norm after the last finished iteration
     double sum_r2;
-    int iters;           // iterations finished
-    int converged;       // set by the iteration that met the threshold
+    int iters;           // iterations finished                 (iters, converged: one aligned 64-bit word,
+    int converged;       // set by the iteration that met the threshold   read with one load by the persistent sweep)
     unsigned int ticket; // last-block election
     int pad;
     SorCtl* mirror;      // zero-copy twin in pinned host memory (NULL in the twin itself)
 };
+
+static_assert(offsetof(SorCtl, iters) % 8 == 0 && offsetof(SorCtl, converged) == offsetof(SorCtl, iters) + 4, "SorCtl: {iters, converged} must form one 64-bit word");
 
 #ifdef __CUDACC__
 // Publish the control block to its pinned-host twin (one thread).  The host polls `converged` /

@@ -52,6 +52,16 @@
 #define SOR_STAGE_BYTES (4 * SOR_ROW_BYTES)   // p even row, p odd row, RHS even row, RHS odd row
 #define SOR_WARP_SMEM (SOR_NST * SOR_STAGE_BYTES)
 #define SOR_SMEM_BYTES (SOR_WARPS * SOR_WARP_SMEM + SOR_WARPS * 2 * SOR_NST * 8)   // rings + FULL/EMPTY mbarriers
+// Rows behind the arriving row j at which the black update and the residual run (red is always j-1).
+// 2 / 3 is the tightest schedule (each phase uses what the previous one produced in the same step);
+// 3 / 5 makes the three phases of a step independent of each other (more instruction-level
+// parallelism per warp at the price of two more rows in the register window).
+#ifndef SOR_LAG_BLACK
+#define SOR_LAG_BLACK 2
+#endif
+#ifndef SOR_LAG_RES
+#define SOR_LAG_RES 3
+#endif
 
 struct SorStreamArgs {
     const double* __restrict__ pin;
@@ -241,10 +251,15 @@ __device__ __forceinline__ void issue_pair(TaskCtx& t, int st, uint32_t empty_ph
 template <int QM, bool EX, bool EY, int S>
 __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], const int sb, TaskCtx& t,
                                          const SorCoef& kf, const LaneGeom& lg, double& acc, bool& ok) {
-    constexpr int sE = S & 7, sD = (S + 7) & 7, sC = (S + 6) & 7, sB = (S + 5) & 7, sA = (S + 4) & 7;
+    constexpr int LB = SOR_LAG_BLACK, LR = SOR_LAG_RES;
+    constexpr int sE = S & 7, sD = (S + 7) & 7, sC = (S + 6) & 7;                 // rows j, j-1, j-2
+    constexpr int sK = (S + 16 - LB) & 7, sKn = (S + 17 - LB) & 7, sKs = (S + 15 - LB) & 7;   // black row, north, south
+    constexpr int sR = (S + 16 - LR) & 7, sRn = (S + 17 - LR) & 7, sRs = (S + 15 - LR) & 7;   // residual row, north, south
     constexpr int st = (S >> 1) & (SOR_NST - 1);
-    constexpr int k0 = (S & 1) ? 1 : 0;     // cells updated this step: columns k0 and k0 + 2
+    constexpr int k0 = (S & 1) ? 1 : 0;     // red cells of row j-1: columns k0 and k0 + 2
     constexpr int k1 = k0 + 2;
+    constexpr int b0 = ((S + LB) & 1) ? 1 : 0;   // black cells of row j-LB
+    constexpr int b1 = b0 + 2;
     const unsigned FULL = 0xffffffffu;
     const int j = t.jstart + sb + S;
 
@@ -310,34 +325,34 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
         if (row_in && (!EX || lg.inner[k1])) { X[k1] = u1; if (EX) ok = ok && ok1; }
     }
 
-    // ---- colour 1 (black) on row C = j-2; neighbours B (j-3, final) and D (j-1, red done)
+    // ---- colour 1 (black) on row K = j-LB; neighbours: south (final) and north (red done, black cells still old)
     {
-        const int r = j - 2;
+        const int r = j - LB;
         const bool row_in = !EY || ((r >= t.rlo) && (r <= t.rhi));
-        double (&X)[4] = P[sC];
+        double (&X)[4] = P[sK];
         if (EX) refresh_ghost_columns(X, lg);                           // main.cu:694
         if (EY) {
             if (r == 1 && t.wall_bottom) {
 #pragma unroll
-                for (int k = 0; k < 4; k++) P[sB][k] = X[k];
+                for (int k = 0; k < 4; k++) P[sKs][k] = X[k];
             }
             if (r == t.nj && t.wall_top) {
 #pragma unroll
-                for (int k = 0; k < 4; k++) P[sD][k] = X[k];
+                for (int k = 0; k < 4; k++) P[sKn][k] = X[k];
             }
         }
         double xw = 0.0, xe = 0.0;
-        if (k0 == 0) xw = __shfl_up_sync(FULL, X[3], 1);
+        if (b0 == 0) xw = __shfl_up_sync(FULL, X[3], 1);
         else xe = __shfl_down_sync(FULL, X[0], 1);
-        const double w0 = (k0 == 0) ? xw : X[(k0 + 3) & 3];
-        const double e0 = X[k0 + 1];
-        const double w1 = X[k1 - 1];
-        const double e1 = (k1 == 3) ? xe : X[(k1 + 1) & 3];
+        const double w0 = (b0 == 0) ? xw : X[(b0 + 3) & 3];
+        const double e0 = X[b0 + 1];
+        const double w1 = X[b1 - 1];
+        const double e1 = (b1 == 3) ? xe : X[(b1 + 1) & 3];
         bool ok0 = true, ok1 = true;
-        const double u0 = sor_cell_q<QM>(X[k0], e0, w0, P[sD][k0], P[sB][k0], R[sC][k0], kf, EX ? ok0 : ok);
-        const double u1 = sor_cell_q<QM>(X[k1], e1, w1, P[sD][k1], P[sB][k1], R[sC][k1], kf, EX ? ok1 : ok);
-        if (row_in && (!EX || lg.inner[k0])) { X[k0] = u0; if (EX) ok = ok && ok0; }
-        if (row_in && (!EX || lg.inner[k1])) { X[k1] = u1; if (EX) ok = ok && ok1; }
+        const double u0 = sor_cell_q<QM>(X[b0], e0, w0, P[sKn][b0], P[sKs][b0], R[sK][b0], kf, EX ? ok0 : ok);
+        const double u1 = sor_cell_q<QM>(X[b1], e1, w1, P[sKn][b1], P[sKs][b1], R[sK][b1], kf, EX ? ok1 : ok);
+        if (row_in && (!EX || lg.inner[b0])) { X[b0] = u0; if (EX) ok = ok && ok0; }
+        if (row_in && (!EX || lg.inner[b1])) { X[b1] = u1; if (EX) ok = ok && ok1; }
         if (EX && (!EY || (r >= t.jc0 && r <= t.jc1))) {
             // ghost columns of the final row, as the refresh before colour 1 left them (main.cu:694):
             // the west ghost lives in the halo lane 0 of the first strip, the east ghost in an owner
@@ -350,7 +365,7 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
                 else t.pout_row[3] = X[3];
             }
         }
-        // row j-2 is final: store it (one full 32-byte sector per lane)
+        // the row is final: store it (one full 32-byte sector per lane)
         if (lg.owner && (!EY || (r >= t.jc0 && r <= t.jc1))) {
             double2* q = reinterpret_cast<double2*>(t.pout_row);
             q[0] = make_double2(X[0], X[1]);
@@ -360,13 +375,13 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
                 // before the black update, held in the window slots B / D)
                 if (r == 1 && t.wall_bottom) {
                     double2* h = reinterpret_cast<double2*>(t.pout_row - t.pitch);
-                    h[0] = make_double2(P[sB][0], P[sB][1]);
-                    h[1] = make_double2(P[sB][2], P[sB][3]);
+                    h[0] = make_double2(P[sKs][0], P[sKs][1]);
+                    h[1] = make_double2(P[sKs][2], P[sKs][3]);
                 }
                 if (r == t.nj && t.wall_top) {
                     double2* h = reinterpret_cast<double2*>(t.pout_row + t.pitch);
-                    h[0] = make_double2(P[sD][0], P[sD][1]);
-                    h[1] = make_double2(P[sD][2], P[sD][3]);
+                    h[0] = make_double2(P[sKn][0], P[sKn][1]);
+                    h[1] = make_double2(P[sKn][2], P[sKn][3]);
                 }
                 // y-slab halo: the three rows next to a slab boundary also go straight into the
                 // neighbour's halo rows over NVLink (peer store), SURVEY 8e
@@ -385,10 +400,10 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
         t.pout_row += t.pitch;
     }
 
-    // ---- residual on row B = j-3 with the ghosts as they are (last refreshed before colour 1)
+    // ---- residual on row j-LR (final, as are its neighbours) with the ghosts as they are (last refreshed before colour 1)
     {
-        const int r = j - 3;
-        double (&X)[4] = P[sB];
+        const int r = j - LR;
+        double (&X)[4] = P[sR];
         const double xw = __shfl_up_sync(FULL, X[3], 1);
         const double xe = __shfl_down_sync(FULL, X[0], 1);
         if (!EY || (r >= t.jc0 && r <= t.jc1)) {   // warp-uniform; rows of the chunk are interior rows
@@ -398,7 +413,7 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
                 const double w = (k == 0) ? xw : X[(k + 3) & 3];
                 const double e = (k == 3) ? xe : X[(k + 1) & 3];
                 bool okr = true;
-                const double q = sor_residual_q<QM>(X[k], e, w, P[sC][k], P[sA][k], R[sB][k], kf, EX ? okr : ok);
+                const double q = sor_residual_q<QM>(X[k], e, w, P[sRn][k], P[sRs][k], R[sR][k], kf, EX ? okr : ok);
                 if (!EX || lg.inner[k]) { part = fma(q, q, part); if (EX) ok = ok && okr; }
             }
             acc += part;                           // non-owner lanes are discarded at the end of the task
@@ -419,6 +434,10 @@ __device__ __forceinline__ void sor_block8(double (&P)[8][4], double (&R)[8][4],
     sor_step<QM, EX, EY, 7>(P, R, sb, t, kf, lg, acc, ok);
 }
 
+// Steps of a task: rows jstart .. jc1 + LR arrive (the last ones only to drain the pipeline: the residual of
+// row jc1 runs LR steps after that row arrived; rows above jc1 + 3 are not fetched).
+__device__ __forceinline__ int sor_task_steps(const TaskCtx& t) { return t.jc1 + SOR_LAG_RES - t.jstart + 1; }
+
 // One task = one strip x one chunk of rows, marched bottom to top by one warp.
 template <int QM, bool EX>
 __device__ __forceinline__ double sor_run_task(TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, bool& ok) {
@@ -428,15 +447,15 @@ __device__ __forceinline__ double sor_run_task(TaskCtx& t, const SorCoef& kf, co
 #pragma unroll
         for (int k = 0; k < 4; k++) { P[s][k] = 0.0; R[s][k] = 0.0; }
     double acc = 0.0;
-    const int n_steps = t.jc1 + 3 - t.jstart + 1;            // rows jstart .. jc1+3
+    const int n_steps = sor_task_steps(t);
     for (int sb = 0; sb < n_steps; sb += 8) {
         const int jb = t.jstart + sb;                        // row arriving in the first step of the block
-        // rows touched by the block: residual jb-3 .. jb+4, stores jb-2 .. jb+5, loads jb .. jb+7
+        // rows touched by the block: residual jb-LR .. jb+7-LR, stores jb-LB .. jb+7-LB, loads jb .. jb+7
 #ifdef SOR_NO_LEAN
         const bool clean = false;
 #else
-        const bool clean = (jb - 3 >= t.jc0) && (jb + 5 <= t.jc1) && (jb + 7 <= t.nj) &&
-                           !(t.push_down && jb - 2 <= 3) && !(t.push_up && jb + 5 >= t.nj - 2);
+        const bool clean = (jb - SOR_LAG_RES >= t.jc0) && (jb + 7 - SOR_LAG_BLACK <= t.jc1) && (jb + 7 <= t.nj) &&
+                           !(t.push_down && jb - SOR_LAG_BLACK <= 3) && !(t.push_up && jb + 7 - SOR_LAG_BLACK >= t.nj - 2);
 #endif
         // (a fourth variant <EX, !EY> for the interior rows of the two edge strips was measured: the larger
         //  kernel body costs the LEAN path 10 % -- 5.27 against 5.86 TB/s at 8192^2 -- and was dropped)
@@ -463,7 +482,7 @@ template <bool RECIP>
 __device__ __forceinline__ double sor_task(TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, bool edge_strip,
                                            uint32_t& full_par, uint32_t& empty_par) {
     constexpr int QM = RECIP ? NSB_QUOT_RECIP : NSB_QUOT_TRY;
-    const int n_steps = t.jc1 + 3 - t.jstart + 1;
+    const int n_steps = sor_task_steps(t);
     const double* pin0 = t.pin_next; const double* rhs0 = t.rhs_next; double* pout0 = t.pout_row;
     t.full_par = full_par; t.empty_par = empty_par;
     sor_advance_parities(n_steps, full_par, empty_par);
@@ -552,7 +571,7 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
         t.rhs_next = a.rhs + row_first + coff;
         t.j_next = t.jstart;
         t.j_limit = min(t.jc1 + 3, a.nj + 3);
-        t.pout_row = a.pout + row_first - 2 * a.pitch + coff + (long long)lane * NSB_GROUP;
+        t.pout_row = a.pout + row_first - SOR_LAG_BLACK * a.pitch + coff + (long long)lane * NSB_GROUP;
         t.down_col = a.down_pout + coff + (long long)lane * NSB_GROUP;
         t.up_col = a.up_pout + coff + (long long)lane * NSB_GROUP;
         t.down_nj = a.down_nj;
@@ -727,15 +746,20 @@ __global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
         int stop = 0;
         {
             if (lane == 0) {
+                // {iters, converged} are adjacent: ONE 64-bit acquire load per task reads both (two dependent
+                // L2 round trips per task were ~2 % of the sweep with the convergence test on)
+                const unsigned long long* word = reinterpret_cast<const unsigned long long*>(&a.ctl->iters);
+                unsigned long long w = ld_acquire_gpu(word);
                 if (it >= 2) {
                     const unsigned long long t0 = global_timer_ns();
-                    while (ld_acquire_gpu_s32(&a.ctl->iters) < a.it + it - 1) {
-                        if (a.check && ld_acquire_gpu_s32(&a.ctl->converged)) break;   // nothing closes after convergence
+                    while ((int)(unsigned)(w & 0xffffffffull) < a.it + it - 1) {
+                        if (a.check && (unsigned)(w >> 32)) break;                      // nothing closes after convergence
                         if (*((volatile int*)a.err) || global_timer_ns() - t0 > NSB_SPIN_TIMEOUT_NS) { *((volatile int*)a.err) = 1; stop = 1; break; }
                         __nanosleep(64);
+                        w = ld_acquire_gpu(word);
                     }
                 }
-                if (a.check && ld_acquire_gpu_s32(&a.ctl->converged)) stop = 1;
+                if (a.check && (unsigned)(w >> 32)) stop = 1;
             }
             stop = __shfl_sync(FULLM, stop, 0);
         }
@@ -795,7 +819,7 @@ __global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
         t.rhs_next = a.rhs + row_first + coff;
         t.j_next = t.jstart;
         t.j_limit = min(t.jc1 + 3, a.nj + 3);
-        t.pout_row = pout + row_first - 2 * a.pitch + coff + (long long)lane * NSB_GROUP;
+        t.pout_row = pout + row_first - SOR_LAG_BLACK * a.pitch + coff + (long long)lane * NSB_GROUP;
         t.down_col = pa.down_p[bo] + coff + (long long)lane * NSB_GROUP;
         t.up_col = pa.up_p[bo] + coff + (long long)lane * NSB_GROUP;
         t.down_nj = a.down_nj;
