@@ -199,6 +199,7 @@ int nsb_sor_persist_supported(const nsb_ctx* c);
 cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int n_iter, int check);   // all iterations, one launch
 cudaError_t nsb_launch_sor_lex(nsb_ctx* c, int max_it, int check);       // serial (lexicographic) order, validation
 cudaError_t nsb_launch_sor_simple_iter(nsb_ctx* c, int it, double* p, int check);
+extern "C" int nsb_plan_chunk_rows(int ni, int nj, long long slots, int recip);   // sor_stream.cu, host arithmetic
 SorCoef nsb_make_sor_coef(nsb_ctx* c, long long cells);                  // sor_simple.cu; cells = GLOBAL i_max * j_max
 cudaError_t nsb_launch_sor_finish_ghosts(nsb_ctx* c, double* pfinal, const double* pprev);
 cudaError_t nsb_launch_to_xfast(nsb_ctx* c, const double* src_ref, double* dst);   // [i][j] -> grid

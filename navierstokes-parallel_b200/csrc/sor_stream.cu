@@ -953,6 +953,36 @@ cudaError_t nsb_launch_sor_close(nsb_ctx* c, int it, int check) {
 // ------------------------------------------------------------------------------------------
 // Planning: strips are fixed (120 columns); pick an even chunk height that fills whole waves.
 
+// Chunk height of the persistent sweep (pure host arithmetic, also exported for the CPU tests):
+// `slots` = resident warps of the sweep kernel on the device, recip = reciprocal-product arithmetic.
+extern "C" int nsb_plan_chunk_rows(int ni, int nj, long long slots, int recip) {
+    const long long n_strips = (ni + NSB_STRIP_COLS - 1) / NSB_STRIP_COLS;
+    if (slots < 1) slots = 1;
+    int best = 16;
+    double best_cost = 1e300;
+    // Chunk height of the persistent sweep, 16 .. 128 rows: minimise
+    //     max(tasks per resident warp and iteration, floor) x (rows + 18),   floor = 1.6
+    // -- a task costs its rows plus ~18 row-steps of overhead (3 + 3 halo rows, 8 steps of pipeline
+    // fill, claim / flag waits), and below ~1.6 tasks per warp there is nothing to overlap the
+    // dependency waits between two iterations with (4096^2: 50 chunks of 82 rows = one task per warp
+    // 110 us per iteration, 86 chunks of 48 rows 90 us).  Above 128 rows the tail of a launch and the
+    // balance between SMs suffer (8192^2: 240 rows 298 us, 128 rows 265 us).  Measured optima
+    // (profiles/r1h_chunk_sweep2.txt): 2048^2 16-24, 3072^2 32, 4096^2 48, 5120^2 48-80, 6144^2 64-112,
+    // 7168^2 96-104, 8192^2 120-128; the model picks 16, 28, 50, 78, 112, 128, 128.
+    // With the IEEE division the sweep is instruction bound instead of HBM bound and the balance between
+    // warps counts for more: the measured optima sit at ~2.7 tasks per warp (4096^2 32-48 rows, 5120^2 48,
+    // 6144^2 64-80, 7168^2 90, 8191^2 112; profiles/r1h_chunk_sweep2.txt), hence the higher floor.
+    const double floor_tasks = recip ? 1.6 : 2.6;
+    for (int rows = 16; rows <= 128; rows += 2) {
+        const long long chunks = (nj + rows - 1) / rows;
+        const double per_warp = (double)(chunks * n_strips) / (double)slots;
+        const double cost = (per_warp > floor_tasks ? per_warp : floor_tasks) * (rows + 18);
+        if (cost < best_cost - 1e-9) { best_cost = cost; best = rows; }
+        if (rows >= nj) break;
+    }
+    return best;
+}
+
 void nsb_sor_plan(nsb_ctx* c) {
     const int ni = c->g.ni, nj = c->g.nj;
     // function attributes are per device: set them for the device of every context that is planned
@@ -969,30 +999,10 @@ void nsb_sor_plan(nsb_ctx* c) {
     if (blocks_per_sm < 1) blocks_per_sm = 1;
     const long long slots = (long long)c->sm_count * blocks_per_sm * SOR_WARPS;
     int best = 0;
-    double best_cost = 1e300;
     if (c->O.sor_chunk_rows > 0) {
         best = (c->O.sor_chunk_rows + 1) & ~1;
     } else {
-        // Chunk height of the persistent sweep, 16 .. 128 rows: minimise
-        //     max(tasks per resident warp and iteration, floor) x (rows + 18),   floor = 1.6
-        // -- a task costs its rows plus ~18 row-steps of overhead (3 + 3 halo rows, 8 steps of pipeline
-        // fill, claim / flag waits), and below ~1.6 tasks per warp there is nothing to overlap the
-        // dependency waits between two iterations with (4096^2: 50 chunks of 82 rows = one task per warp
-        // 110 us per iteration, 86 chunks of 48 rows 90 us).  Above 128 rows the tail of a launch and the
-        // balance between SMs suffer (8192^2: 240 rows 298 us, 128 rows 265 us).  Measured optima
-        // (profiles/r1h_chunk_sweep2.txt): 2048^2 16-24, 3072^2 32, 4096^2 48, 5120^2 48-80, 6144^2 64-112,
-        // 7168^2 96-104, 8192^2 120-128; the model picks 16, 28, 50, 78, 112, 128, 128.
-        // With the IEEE division the sweep is instruction bound instead of HBM bound and the balance between
-        // warps counts for more: the measured optima sit at ~2.7 tasks per warp (4096^2 32-48 rows, 5120^2 48,
-        // 6144^2 64-80, 7168^2 90, 8191^2 112; profiles/r1h_chunk_sweep2.txt), hence the higher floor.
-        const double floor_tasks = c->use_recip ? 1.6 : 2.6;
-        for (int rows = 16; rows <= 128; rows += 2) {
-            const long long chunks = (nj + rows - 1) / rows;
-            const double per_warp = (double)(chunks * c->n_strips) / (double)slots;
-            const double cost = (per_warp > floor_tasks ? per_warp : floor_tasks) * (rows + 18);
-            if (cost < best_cost - 1e-9) { best_cost = cost; best = rows; }
-            if (rows >= nj) break;
-        }
+        best = nsb_plan_chunk_rows(ni, nj, slots, c->use_recip ? 1 : 0);
     }
     if (best < 2) best = 2;
     c->chunk_rows = best;
