@@ -511,6 +511,31 @@ def test_full_size_8192_engines_agree_and_nullspace():
     assert abs(outs[2][1] - outs[0][1]) <= 1e-9 * outs[0][1]
 
 
+def test_large_grid_ieee_division_engines_agree():
+    """A large grid whose spacing is not a power of two (4100 x 4090: IEEE division by dx^2 / dy^2, done with the refined
+    reciprocal and the window test of nsb_math.cuh; many chunks of the planned height, partial last strip and chunk):
+    the persistent sweep, the one-launch-per-iteration sweep and the plain validation engine give the same bits
+    on a developed field, zeros included (first cavity step: p is exactly zero away from the lid)."""
+    m = nsb()
+    ni, nj = 4100, 4090
+    outs = []
+    for eng in (m.SOR_STREAM, m.SOR_STREAM_LAUNCH, m.SOR_SIMPLE):
+        P = m.make_params(i_max=ni, j_max=nj, T=1e9, max_it=3)
+        with m.Solver(P, sor_engine=eng) as s:
+            s.step(0.0)                                   # zeros almost everywhere
+            r0 = s.sor_iterations(2)
+            a = s.download(m.P, layout=m.LAYOUT_XFAST)[1:-1, 1:-1].copy()
+            p = np.random.default_rng(77).uniform(-1.0, 1.0, s.shape[::-1])
+            s.upload(m.P, p, layout=m.LAYOUT_XFAST)       # a field without zeros
+            del p
+            r1 = s.sor_iterations(3)
+            outs.append((a, r0, s.download(m.P, layout=m.LAYOUT_XFAST)[1:-1, 1:-1].copy(), r1))
+    for o in outs[1:]:
+        assert np.array_equal(outs[0][0].view(np.int64), o[0].view(np.int64))
+        assert np.array_equal(outs[0][2], o[2])
+        assert abs(outs[0][1] - o[1]) <= 1e-12 * abs(o[1]) and abs(outs[0][3] - o[3]) <= 1e-12 * abs(o[3])
+
+
 def test_reference_cuda_binary_same_stdout(tmp_path):
     """The reference's own CUDA build (src/parallel/*.cu compiled unmodified for sm_100 into
     oracle/_ref/parallel by `make -C oracle refcuda`) on this GPU against build/parallel, with the
