@@ -38,7 +38,7 @@ struct SorCoef {
     double w;        // omega / (2 (1/dx2 + 1/dy2))          main.cu:493,502
     double dx2, dy2; // delta_x^2, delta_y^2
     double rdx2, rdy2;
-    double inv_cells_unused;
+    float qlo_x, qlo_y;  // IEEE-division path: lower edge of the quotient window for dx2 / dy2 (nsb_math.cuh)
     long long cells; // i_max * j_max
 };
 

@@ -5,6 +5,9 @@
 // fused engines against an independent GPU implementation at sizes the CPU oracle cannot reach
 // (tests/test_gpu_parity.py); it is coalesced (x fastest) but makes no attempt to be fast.
 #include "nsb_internal.h"
+#include <math.h>
+#include <string.h>
+
 #include "nsb_math.cuh"
 
 // ---- SOR entry: threshold from the cached sum p^2 (replaces calculate_L2_norm_device,
@@ -112,13 +115,30 @@ __global__ void rcp_refine_kernel(double dx2, double dy2) {
     g_rcp_out[1] = nsb_rcp_refined(dy2);
 }
 
+// Lower edge of the quotient window of nsb_div_try for divisor d, as the binary32 pattern its compare uses on the
+// HIGH WORD of the quotient: above the compiler's own edge (high word 0x00100000) and above 2^-968 / d, so that a
+// quotient inside the window comes from an |x| >= 2^-969 (the compiler's edge for the dividend).  A divisor outside
+// 2^-500 .. 2^500 gets +inf: every quotient then takes the real division.
+static float quot_window_lo(double d) {
+    uint32_t h = 0x00100000u;
+    if (!(d > ldexp(1.0, -500) && d < ldexp(1.0, 500))) return INFINITY;
+    const double lo = ldexp(1.0, -968) / d;
+    uint64_t bits;
+    memcpy(&bits, &lo, sizeof bits);
+    const uint32_t hi = (uint32_t)(bits >> 32) + 1u;
+    if (hi > h) h = hi;
+    float f;
+    memcpy(&f, &h, sizeof f);
+    return f;
+}
+
 SorCoef nsb_make_sor_coef(nsb_ctx* c, long long cells) {
     SorCoef k;
     const double dx2 = c->dx * c->dx, dy2 = c->dy * c->dy;
     k.om1 = 1.0 - c->P.omega;
     k.w = c->P.omega / (2.0 * (1.0 / dx2 + 1.0 / dy2));
     k.dx2 = dx2; k.dy2 = dy2; k.rdx2 = 1.0 / dx2; k.rdy2 = 1.0 / dy2;
-    k.inv_cells_unused = 0.0;
+    k.qlo_x = quot_window_lo(dx2); k.qlo_y = quot_window_lo(dy2);
     k.cells = cells;
     if (!c->use_recip) {
         if (!c->rcp_valid || c->rcp_key[0] != dx2 || c->rcp_key[1] != dy2) {
@@ -278,7 +298,7 @@ __device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
     z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
     return z ^ (z >> 31);
 }
-__global__ void divcheck_kernel(double d1, double d2, double r1, double r2, long long n, unsigned long long seed, int mode,
+__global__ void divcheck_kernel(double d1, double d2, double r1, double r2, float lo1, float lo2, long long n, unsigned long long seed, int mode,
                                 unsigned long long* bad, double* first_bad) {
     unsigned long long local = 0;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
@@ -309,7 +329,7 @@ __global__ void divcheck_kernel(double d1, double d2, double r1, double r2, long
         // inside the window (w1 / w2 stay true) the three-operation quotient must BE the division;
         // outside, the callers fall back to nsb_div_full
         bool w1 = true, w2 = true;
-        double q1 = nsb_div_try(x1, d1, r1, w1), q2 = nsb_div_try(x2, d2, r2, w2);
+        double q1 = nsb_div_try(x1, d1, r1, lo1, w1), q2 = nsb_div_try(x2, d2, r2, lo2, w2);
         if (!w1) q1 = nsb_div_full(x1, d1);
         if (!w2) q2 = nsb_div_full(x2, d2);
         const double t1 = __ddiv_rn(x1, d1), t2 = __ddiv_rn(x2, d2);
@@ -333,7 +353,7 @@ extern "C" int nsb_debug_divcheck(double d1, double d2, long long n, unsigned lo
     rcp_refine_kernel<<<1, 1>>>(d1, d2);
     double r[2] = {0.0, 0.0};
     cudaMemcpyFromSymbol(r, g_rcp_out, sizeof r);
-    divcheck_kernel<<<148 * 8, 256>>>(d1, d2, r[0], r[1], n, seed, mode, bad, fb);
+    divcheck_kernel<<<148 * 8, 256>>>(d1, d2, r[0], r[1], quot_window_lo(d1), quot_window_lo(d2), n, seed, mode, bad, fb);
     unsigned long long hb[2] = {0, 0};
     double hf[2] = {0.0, 0.0};
     cudaError_t e = cudaMemcpy(hb, bad, 16, cudaMemcpyDeviceToHost);
