@@ -30,6 +30,12 @@
 //   - residual: per-warp partial (fixed order), last block of the grid adds the partials in a fixed
 //     order, takes sqrt(sum/(i_max*j_max)) (main.cu:588), compares with eps*(norm_p+1.5)
 //     (main.cu:713) and raises the device-side converged flag; later launches exit at once.
+//   - two kernels share this code: sor_stream_kernel (one launch per iteration: validation, and
+//     several slabs emulated on one GPU) and sor_persist_kernel (the product: all iterations of a
+//     solve in one launch, tasks claimed from a global counter and ordered by per-task flags; see
+//     the comment above it).  Both are instantiated for RECIP (reciprocal product / IEEE division
+//     with the refined reciprocal, nsb_math.cuh) and for MULTI (one slab / several): every body
+//     that is not needed is left out, because the kernel is co-limited by the instruction cache.
 #include <string.h>
 
 #include "nsb_internal.h"
