@@ -49,10 +49,16 @@
 #ifndef SOR_MIN_BLOCKS
 #define SOR_MIN_BLOCKS 3
 #endif
-#ifndef SOR_LOG_NST
-#define SOR_LOG_NST 1          // log2(row-pair stages per warp)
+// Steps per unrolled block (= slots of the register window, a compile-time ring) and row-pair stages of the
+// per-warp TMA ring.  SOR_BLK must be a multiple of 2 * SOR_NST and larger than SOR_LAG_RES + 1.
+#ifndef SOR_BLK
+#define SOR_BLK 8
 #endif
-#define SOR_NST (1 << SOR_LOG_NST)
+#ifndef SOR_NST
+#define SOR_NST 2
+#endif
+#define SOR_USES_PER_BLK (SOR_BLK / 2 / SOR_NST)   // times a stage is filled and read per block
+static_assert(SOR_BLK % (2 * SOR_NST) == 0, "SOR_BLK must be a multiple of 2 * SOR_NST");
 #define SOR_ROW_BYTES 1024     // 32 lanes x 32 B
 #define SOR_ROW_DBL (SOR_ROW_BYTES / 8)
 #define SOR_STAGE_BYTES (4 * SOR_ROW_BYTES)   // p even row, p odd row, RHS even row, RHS odd row
@@ -255,13 +261,15 @@ __device__ __forceinline__ void issue_pair(TaskCtx& t, int st, uint32_t empty_ph
 //       is USED left the window of the three-operation division (pad / ghost columns of an edge strip may
 //       hold anything and are not counted).
 template <int QM, bool EX, bool EY, int S>
-__device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], const int sb, TaskCtx& t,
+__device__ __forceinline__ void sor_step(double (&P)[SOR_BLK][4], double (&R)[SOR_BLK][4], const int sb, const uint32_t use0, TaskCtx& t,
                                          const SorCoef& kf, const LaneGeom& lg, double& acc, bool& ok) {
     constexpr int LB = SOR_LAG_BLACK, LR = SOR_LAG_RES;
-    constexpr int sE = S & 7, sD = (S + 7) & 7, sC = (S + 6) & 7;                 // rows j, j-1, j-2
-    constexpr int sK = (S + 16 - LB) & 7, sKn = (S + 17 - LB) & 7, sKs = (S + 15 - LB) & 7;   // black row, north, south
-    constexpr int sR = (S + 16 - LR) & 7, sRn = (S + 17 - LR) & 7, sRs = (S + 15 - LR) & 7;   // residual row, north, south
-    constexpr int st = (S >> 1) & (SOR_NST - 1);
+    constexpr int NS = SOR_BLK;                                                    // window slots
+    static_assert(LR + 2 <= NS, "register window too small for the residual lag");
+    constexpr int sE = S % NS, sD = (S + NS - 1) % NS, sC = (S + NS - 2) % NS;     // rows j, j-1, j-2
+    constexpr int sK = (S + 2 * NS - LB) % NS, sKn = (S + 2 * NS + 1 - LB) % NS, sKs = (S + 2 * NS - 1 - LB) % NS;   // black row, north, south
+    constexpr int sR = (S + 2 * NS - LR) % NS, sRn = (S + 2 * NS + 1 - LR) % NS, sRs = (S + 2 * NS - 1 - LR) % NS;   // residual row, north, south
+    constexpr int st = (S >> 1) % SOR_NST;
     constexpr int k0 = (S & 1) ? 1 : 0;     // red cells of row j-1: columns k0 and k0 + 2
     constexpr int k1 = k0 + 2;
     constexpr int b0 = ((S + LB) & 1) ? 1 : 0;   // black cells of row j-LB
@@ -272,7 +280,7 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
     // ---- row j (p and RHS) from the ring into registers; after the odd row of a pair the stage
     //      goes back to the TMA engine
     {
-        const uint32_t ph = ((uint32_t)(sb + S) >> (1 + SOR_LOG_NST)) & 1u;   // use count of the stage, mod 2
+        const uint32_t ph = (use0 + (uint32_t)((S >> 1) / SOR_NST)) & 1u;      // use count of the stage, mod 2
         if ((S & 1) == 0) {
             mbar_wait(t.bar_base + st * 8, ph ^ t.full_par);
 #ifdef SOR_SYNC_EACH_STEP
@@ -427,17 +435,19 @@ __device__ __forceinline__ void sor_step(double (&P)[8][4], double (&R)[8][4], c
     }
 }
 
+template <int QM, bool EX, bool EY, int S>
+__device__ __forceinline__ void sor_steps_from(double (&P)[SOR_BLK][4], double (&R)[SOR_BLK][4], const int sb, const uint32_t use0,
+                                               TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, double& acc, bool& ok) {
+    if constexpr (S < SOR_BLK) {
+        sor_step<QM, EX, EY, S>(P, R, sb, use0, t, kf, lg, acc, ok);
+        sor_steps_from<QM, EX, EY, S + 1>(P, R, sb, use0, t, kf, lg, acc, ok);
+    }
+}
+// One unrolled block of SOR_BLK steps; use0 = times every ring stage has been used before this block.
 template <int QM, bool EX, bool EY>
-__device__ __forceinline__ void sor_block8(double (&P)[8][4], double (&R)[8][4], const int sb, TaskCtx& t,
-                                           const SorCoef& kf, const LaneGeom& lg, double& acc, bool& ok) {
-    sor_step<QM, EX, EY, 0>(P, R, sb, t, kf, lg, acc, ok);
-    sor_step<QM, EX, EY, 1>(P, R, sb, t, kf, lg, acc, ok);
-    sor_step<QM, EX, EY, 2>(P, R, sb, t, kf, lg, acc, ok);
-    sor_step<QM, EX, EY, 3>(P, R, sb, t, kf, lg, acc, ok);
-    sor_step<QM, EX, EY, 4>(P, R, sb, t, kf, lg, acc, ok);
-    sor_step<QM, EX, EY, 5>(P, R, sb, t, kf, lg, acc, ok);
-    sor_step<QM, EX, EY, 6>(P, R, sb, t, kf, lg, acc, ok);
-    sor_step<QM, EX, EY, 7>(P, R, sb, t, kf, lg, acc, ok);
+__device__ __forceinline__ void sor_block8(double (&P)[SOR_BLK][4], double (&R)[SOR_BLK][4], const int sb, const uint32_t use0,
+                                           TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, double& acc, bool& ok) {
+    sor_steps_from<QM, EX, EY, 0>(P, R, sb, use0, t, kf, lg, acc, ok);
 }
 
 // Steps of a task: rows jstart .. jc1 + LR arrive (the last ones only to drain the pipeline: the residual of
@@ -447,34 +457,35 @@ __device__ __forceinline__ int sor_task_steps(const TaskCtx& t) { return t.jc1 +
 // One task = one strip x one chunk of rows, marched bottom to top by one warp.
 template <int QM, bool EX>
 __device__ __forceinline__ double sor_run_task(TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, bool& ok) {
-    double P[8][4], R[8][4];
+    double P[SOR_BLK][4], R[SOR_BLK][4];
 #pragma unroll
-    for (int s = 0; s < 8; s++)
+    for (int s = 0; s < SOR_BLK; s++)
 #pragma unroll
         for (int k = 0; k < 4; k++) { P[s][k] = 0.0; R[s][k] = 0.0; }
     double acc = 0.0;
     const int n_steps = sor_task_steps(t);
-    for (int sb = 0; sb < n_steps; sb += 8) {
+    uint32_t use0 = 0u;
+    for (int sb = 0; sb < n_steps; sb += SOR_BLK, use0 += SOR_USES_PER_BLK) {
         const int jb = t.jstart + sb;                        // row arriving in the first step of the block
-        // rows touched by the block: residual jb-LR .. jb+7-LR, stores jb-LB .. jb+7-LB, loads jb .. jb+7
+        // rows touched by the block (B = SOR_BLK): residual jb-LR .. jb+B-1-LR, stores jb-LB .. jb+B-1-LB, loads jb .. jb+B-1
 #ifdef SOR_NO_LEAN
         const bool clean = false;
 #else
-        const bool clean = (jb - SOR_LAG_RES >= t.jc0) && (jb + 7 - SOR_LAG_BLACK <= t.jc1) && (jb + 7 <= t.nj) &&
-                           !(t.push_down && jb - SOR_LAG_BLACK <= 3) && !(t.push_up && jb + 7 - SOR_LAG_BLACK >= t.nj - 2);
+        const bool clean = (jb - SOR_LAG_RES >= t.jc0) && (jb + SOR_BLK - 1 - SOR_LAG_BLACK <= t.jc1) && (jb + SOR_BLK - 1 <= t.nj) &&
+                           !(t.push_down && jb - SOR_LAG_BLACK <= 3) && !(t.push_up && jb + SOR_BLK - 1 - SOR_LAG_BLACK >= t.nj - 2);
 #endif
         // (a fourth variant <EX, !EY> for the interior rows of the two edge strips was measured: the larger
         //  kernel body costs the LEAN path 10 % -- 5.27 against 5.86 TB/s at 8192^2 -- and was dropped)
-        if (EX) sor_block8<QM, true, true>(P, R, sb, t, kf, lg, acc, ok);
-        else if (clean && QM != NSB_QUOT_FULL) sor_block8<QM, false, false>(P, R, sb, t, kf, lg, acc, ok);
-        else sor_block8<QM, false, true>(P, R, sb, t, kf, lg, acc, ok);
+        if (EX) sor_block8<QM, true, true>(P, R, sb, use0, t, kf, lg, acc, ok);
+        else if (clean && QM != NSB_QUOT_FULL) sor_block8<QM, false, false>(P, R, sb, use0, t, kf, lg, acc, ok);
+        else sor_block8<QM, false, true>(P, R, sb, use0, t, kf, lg, acc, ok);
     }
     return lg.owner ? acc : 0.0;
 }
 
 // Phase parities of a warp's mbarriers after one task of n_steps rows (see sor_persist_kernel).
 __device__ __forceinline__ void sor_advance_parities(int n_steps, uint32_t& full_par, uint32_t& empty_par) {
-    const uint32_t pairs_per_stage = (uint32_t)(((n_steps + 7) / 8) * 4 / SOR_NST);
+    const uint32_t pairs_per_stage = (uint32_t)(((n_steps + SOR_BLK - 1) / SOR_BLK) * SOR_USES_PER_BLK);
     full_par ^= (pairs_per_stage + 1u) & 1u;
     empty_par ^= pairs_per_stage & 1u;
 }
