@@ -146,8 +146,8 @@ SorCoef nsb_make_sor_coef(nsb_ctx* c, long long cells) {
             double out[2] = {0.0, 0.0};
             cudaError_t e = cudaMemcpyFromSymbolAsync(out, g_rcp_out, sizeof out, 0, cudaMemcpyDeviceToHost, c->stream);
             if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
-            // a failed refinement leaves the plain reciprocal: nsb_div_const then still returns the
-            // IEEE quotient whenever its three steps do (the error surfaces at the next launch)
+            // a failed refinement (a CUDA error, which the next launch reports) closes the quotient window
+            // below: every quotient then takes the real division
             if (e == cudaSuccess && out[0] != 0.0 && out[1] != 0.0) {
                 c->rcp_key[0] = dx2; c->rcp_key[1] = dy2;
                 c->rcp_val[0] = out[0]; c->rcp_val[1] = out[1];
@@ -155,6 +155,7 @@ SorCoef nsb_make_sor_coef(nsb_ctx* c, long long cells) {
             }
         }
         if (c->rcp_valid) { k.rdx2 = c->rcp_val[0]; k.rdy2 = c->rcp_val[1]; }
+        else { k.qlo_x = INFINITY; k.qlo_y = INFINITY; }
     }
     return k;
 }
