@@ -90,6 +90,18 @@ class ClockSampler:
                 "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def host_cpu():
+    model = "unknown"
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.lower().startswith("model name"):
+                model = line.split(":", 1)[1].strip()
+                break
+    except Exception:
+        pass
+    return {"cpu_model": model, "nproc": os.cpu_count()}
+
+
 # ----------------------------------------------------------------------------- CPU reference leg
 def cpu_reference_sor(size, iters_per_step, steps, warmup):
     """Times the reference's own serial SOR (src/serial/integration.c:129-173, compiled unmodified
@@ -120,12 +132,101 @@ def cpu_reference_sor(size, iters_per_step, steps, warmup):
         run()
     el = time.perf_counter() - t0
     lups = float(steps) * iters_per_step * ni * nj
-    return {"value": lups / el / 1e6, "unit": "MLUPS", "cores": 1, "kind": kind,
+    return {"value": lups / el / 1e6, "unit": "MLUPS", "cores": 1, "kind": kind, "host": host_cpu(),
             "sample": f"{steps} x SOR({iters_per_step} lexicographic sweeps, residual every sweep) on the "
                       f"{size}x{size} cavity RHS, {'oracle/_ref/libnsref.so (unmodified reference serial SOR)' if kind == 'reference' else 'oracle port'}, "
                       f"single thread (the reference is single-threaded), {el:.1f} s",
             "seconds": el, "ms_per_step": el / steps * 1e3}
 
+
+
+# ----------------------------------------------------------------------------- parity gate
+def parity_gate(m, rank, world, local, dist, ni=2048, rows_per_gpu=2048, iters=30):
+    """Runs BEFORE the timed region, at every N, through the SAME engine the timing uses (persistent sweep, the
+    multi-slab kernel with in-flight halo flags at N > 1, the timed run's chunk height): one whole time step of a
+    ni x (rows_per_gpu * N) cavity with max_it = `iters` (BC, F/G, RHS, `iters` red+black+residual iterations,
+    velocity update) and `iters` more bare iterations.  Rank 0 then solves the same GLOBAL problem on one slab and
+    with the CPU oracle (all host cores; the oracle is the checker, never the thing timed) and compares, bit for bit,
+    sha256 of every rank's rows of u, v, p, plus dt and the two residuals (hex).  A mismatch ends the run non-zero."""
+    import hashlib
+    import torch
+    nj = rows_per_gpu * world
+    P = m.make_params(problem=1, f=1.0, i_max=ni, j_max=nj, a=1.0, b=float(nj) / float(ni), T=1.0e9, Re=1000.0,
+                      g_x=0.0, g_y=0.0, tau=1.0, omega=1.7, epsilon=1e-4, max_it=iters, n_print=1)
+    ch = 128
+
+    def digest(rows):           # rows: C-contiguous (n_rows, ni + 2) block, x fastest
+        return hashlib.sha256(np.ascontiguousarray(rows).tobytes()).hexdigest()
+
+    def run(s, j_lo, nj_loc):
+        info = s.step(0.0)
+        res2 = s.sor_iterations(iters)
+        out = {"dt": float(info["dt"]).hex(), "res": float(info["res"]).hex(), "res2": float(res2).hex(),
+               "iters": info["sor_iters"], "j_lo": j_lo, "nj": nj_loc}
+        for name, f in (("u", m.U), ("v", m.V), ("p", m.P)):
+            a = s.download(f, layout=m.LAYOUT_XFAST)
+            out[name] = digest(a[1:nj_loc + 1])
+        return out
+
+    t0 = time.time()
+    if world == 1:
+        mine = None
+    else:
+        s = m.SlabSolver(P, rank, world, m.torch_all_gather(), device=local, chunk_rows=ch)
+        mine = run(s, s.j_lo, s.nj)
+        engine = "sor_persist_kernel<*, MULTI=1>, %d slabs, chunk_rows %d" % (world, s.chunk_rows)
+        dist.barrier()
+        s.close()
+        blobs = m.torch_all_gather()(json.dumps(mine).encode().ljust(1024))
+        parts = [json.loads(b.decode().strip()) for b in blobs]
+    result = None
+    if rank == 0:
+        # the same global problem on ONE slab (single-slab instantiation of the same sweep)
+        with m.Solver(P, device=local, sor_engine=m.SOR_STREAM, chunk_rows=ch) as s1:
+            info = s1.step(0.0)
+            res2 = s1.sor_iterations(iters)
+            one = {"dt": float(info["dt"]).hex(), "res": float(info["res"]).hex(), "res2": float(res2).hex(),
+                   "iters": info["sor_iters"]}
+            F1 = {name: s1.download(f, layout=m.LAYOUT_XFAST) for name, f in (("u", m.U), ("v", m.V), ("p", m.P))}
+        if world == 1:
+            engine = "sor_persist_kernel<*, MULTI=0>, chunk_rows %d" % ch
+            parts = []
+        ok_slabs = True
+        for q in parts:
+            for k in ("dt", "res", "res2", "iters"):
+                ok_slabs = ok_slabs and (q[k] == one[k])
+            for name in ("u", "v", "p"):
+                ok_slabs = ok_slabs and (q[name] == digest(F1[name][q["j_lo"] + 1:q["j_lo"] + q["nj"] + 1]))
+        # CPU oracle: the same step + iterations, all host cores for the sweeps
+        from oracle import binding as ob
+        L = ob.lib()
+        oP = ob.make_params(**{k: getattr(P, k) for k, _ in ob.Params._fields_})
+        dx, dy = P.a / ni, P.b / nj
+        u, v, F, G, R, pp = (ob.zeros(oP) for _ in range(6))
+        dt, gamma = C.c_double(), C.c_double()
+        L.orc_dt_gamma(C.byref(oP), dx, dy, 0.0, 0.0, C.byref(dt), C.byref(gamma))
+        L.orc_apply_bc(C.byref(oP), 0.0, ob._ptr(u), ob._ptr(v))
+        L.orc_FG(ob._ptr(F), ob._ptr(G), ob._ptr(u), ob._ptr(v), ni, nj, P.Re, 0.0, 0.0, dt.value, dx, dy, gamma.value)
+        L.orc_RHS(ob._ptr(R), ob._ptr(F), ob._ptr(G), ni, nj, dt.value, dx, dy)
+        _, _, ores = ob.sor_rb_omp(pp, R, dx, dy, P.omega, 0.0, iters)
+        L.orc_update_uv(ob._ptr(u), ob._ptr(v), ob._ptr(F), ob._ptr(G), ob._ptr(pp), ni, nj, dt.value, dx, dy)
+        _, _, ores2 = ob.sor_rb_omp(pp, R, dx, dy, P.omega, 0.0, iters)
+        ok_orc = (float(dt.value).hex() == one["dt"]) and one["iters"] == iters
+        ok_orc = ok_orc and abs(float.fromhex(one["res"]) - ores) <= 1e-12 * ores and abs(float.fromhex(one["res2"]) - ores2) <= 1e-12 * ores2
+        for name, arr in (("u", u), ("v", v), ("p", pp)):
+            ok_orc = ok_orc and np.array_equal(F1[name][1:nj + 1, 1:ni + 1], arr.T[1:nj + 1, 1:ni + 1])
+        result = {"checked": True, "ok": bool(ok_slabs and ok_orc), "engine": engine,
+                  "case": "%dx%d cavity, 1 whole step (max_it %d) + %d iterations" % (ni, nj, iters, iters),
+                  "vs": (["single-slab run of the same global problem (sha256 of u, v, p rows per rank, dt / residual hex)"] if world > 1 else []) +
+                        ["oracle/liboracle.so (orc_FG, orc_RHS, orc_SOR_rb_omp, orc_update_uv): u, v, p bit-exact, residuals 1e-12"],
+                  "ok_vs_single_slab": bool(ok_slabs) if world > 1 else None, "ok_vs_oracle": bool(ok_orc),
+                  "seconds": round(time.time() - t0, 1)}
+    if world > 1:
+        flag = torch.tensor([1 if (result is None or result["ok"]) else 0], device="cuda")
+        dist.broadcast(flag, 0)
+        if int(flag.item()) == 0 and rank != 0:
+            raise SystemExit(3)
+    return result
 
 # ----------------------------------------------------------------------------- main
 def main():
@@ -143,6 +244,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--engine", type=int, default=0)
     ap.add_argument("--chunk-rows", type=int, default=0)
+    ap.add_argument("--no-parity", action="store_true", help="skip the parity gate that runs before the timed region")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -178,9 +280,12 @@ def main():
         line = {"impl": "reference", "metric": "sor_mlups", "value": b["value"], "unit": "MLUPS", "n_gpus": args.gpus,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": b["ms_per_step"], "higher_is_better": True,
                 "scaling": scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
-                "cpu_baseline": {k: b[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "cpu_baseline": {k: b[k] for k in ("value", "unit", "cores", "kind", "sample", "host")},
                 "e2e": {"value": b["value"], "unit": "MLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                "gpu_launches": 0}
+                "gpu_launches": 0,
+                "reference_arm_note": (f"the reference has no multi-GPU / multi-threaded path: this arm always times its serial "
+                                       f"SOR on ONE host core on a {size}x{size} grid (bounded sample), whatever --gpus says; "
+                                       f"at N > 1 the GPU arm's grid is {ni}x{nj}")}
         print(json.dumps(line))
         return 0
 
@@ -212,6 +317,15 @@ def main():
         tt = torch.tensor([x], device="cuda", dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.SUM)
         return float(tt.item())
+
+    parity = {"checked": False}
+    if not args.no_parity:
+        parity = parity_gate(m, rank, world, local, dist)
+        if rank == 0 and not parity["ok"]:
+            print(json.dumps({"metric": "sor_mlups", "value": None, "n_gpus": world, "parity": parity,
+                              "error": "parity gate failed: nothing was timed"}))
+            sys.exit(3)
+        barrier()
 
     P = m.make_params(problem=1, f=1.0, i_max=ni, j_max=nj, a=1.0, b=float(nj) / float(ni), T=1.0e9, Re=1000.0,
                       g_x=0.0, g_y=0.0, tau=1.0, omega=1.7, epsilon=1e-4, max_it=max_it, n_print=1)
@@ -269,13 +383,16 @@ def main():
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = 24.0 * cells_local / (k_ms * 1e-3) / 1e9
-    traffic = None
+    traffic, traffic_src = None, None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "sor_stream_traffic.json"))).get("dram_bytes_per_iteration") * n_k
+        tj = json.load(open(os.path.join(ROOT, "profiles", "sor_stream_traffic.json")))
+        traffic = tj.get("dram_bytes_per_iteration") * n_k
+        traffic_src = "static, not measured in this run: " + tj.get("source", "profiles/sor_stream_traffic.json")
     except Exception:
         pass
     roofline = {"bound": "hbm", "kernel": "sor_persist_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic if (world == 1 and size == 8192) else None,
+                "traffic_source": traffic_src if (world == 1 and size == 8192) else None,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
                 "iterations_per_launch": n_k, "algorithmic_bytes_per_launch": 24.0 * cells_local * n_k,
                 "launch_ms": k_ms * n_k, "ms_per_iteration": k_ms,
@@ -339,7 +456,7 @@ def main():
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         b = cpu_reference_sor(size, 2 if size >= 4096 else max(2, int(2e8 / cells)), 8 if size >= 4096 else 5, 1)
-        cpu = {k: b[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        cpu = {k: b[k] for k in ("value", "unit", "cores", "kind", "sample", "host")}
 
     if rank == 0:
         line = {"metric": "sor_mlups", "value": value, "unit": "MLUPS", "n_gpus": world, "steps": args.steps,
@@ -347,7 +464,8 @@ def main():
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
                 "timesteps_per_s": args.steps / (ms * 1e-3), "sor_iters_per_step": iters / max(1, args.steps),
                 "hbm_gbs_whole_step": (80.0 + 24.0 * iters / max(1, args.steps)) * cells * args.steps / (ms * 1e-3) / 1e9,
-                "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
+                "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
+                "parity": parity}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -176,6 +176,7 @@ struct nsb_ctx {
     double sor_seconds;
     long long n_launches;  // kernels of this library enqueued so far (nsb_launch_count)
     int last_sor_engine;
+    int resident_state;    // sor_resident.cu: 0 unknown, 1 usable, -1 this device refused the cluster / cooperative launch
     char err[512];
 };
 

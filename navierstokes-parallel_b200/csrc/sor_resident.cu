@@ -369,10 +369,11 @@ static int resident_plan(const nsb_ctx* c, ResidentPlan* pl) {
     return 1;
 }
 
-static int g_resident_state = 0;   // 0 unknown, 1 usable, -1 the device refused the launch
-
+// c->resident_state (per context, hence per device): 0 unknown, 1 usable, -1 the device refused the launch
+// (MIG slice, a GPC with fewer free SMs than the cluster needs, another SKU): the caller falls through to the
+// streaming sweep within the same solve (step.cu: sor_iterate).
 int nsb_sor_resident_supported(const nsb_ctx* c) {
-    if (g_resident_state < 0) return 0;
+    if (c->resident_state < 0) return 0;
     ResidentPlan pl;
     return resident_plan(c, &pl);
 }
@@ -380,6 +381,7 @@ int nsb_sor_resident_supported(const nsb_ctx* c) {
 cudaError_t nsb_launch_sor_resident(nsb_ctx* c, int max_it, int check) {
     ResidentPlan pl;
     if (!resident_plan(c, &pl)) return cudaErrorNotSupported;
+    if (getenv("NSB_DEBUG_RES_REFUSE")) { c->resident_state = -1; return cudaErrorNotSupported; }   // test hook: a device that refuses
     ResidentArgs a;
     memset(&a, 0, sizeof a);
     a.p = c->pbuf[c->pcur]; a.rhs = c->rhs; a.pitch = c->g.pitch; a.ni = c->g.ni; a.nj = c->g.nj;
@@ -397,11 +399,11 @@ cudaError_t nsb_launch_sor_resident(nsb_ctx* c, int max_it, int check) {
         if (e != cudaSuccess) return e;
         int occ = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, RES_THREADS, pl.smem);
-        if (occ * c->sm_count < pl.n_cta) { g_resident_state = -1; return cudaErrorNotSupported; }
+        if (occ * c->sm_count < pl.n_cta) { c->resident_state = -1; return cudaErrorNotSupported; }
         void* args[] = {&a};
         e = cudaLaunchCooperativeKernel(kern, dim3(pl.n_cta), dim3(RES_THREADS), args, pl.smem, c->stream);
-        if (e != cudaSuccess) { g_resident_state = -1; cudaGetLastError(); return e; }
-        g_resident_state = 1;
+        if (e != cudaSuccess) { c->resident_state = -1; cudaGetLastError(); return e; }
+        c->resident_state = 1;
         return NSB_LAUNCHED(c, 1);
     }
     auto kern = c->use_recip ? sor_resident_kernel<true, false> : sor_resident_kernel<false, false>;
@@ -421,8 +423,14 @@ cudaError_t nsb_launch_sor_resident(nsb_ctx* c, int max_it, int check) {
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = pl.n_cta; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
+    if (c->resident_state == 0) {
+        // can this device co-schedule one cluster of that size with that much shared memory at all?
+        int n_clusters = 0;
+        e = cudaOccupancyMaxActiveClusters(&n_clusters, kern, &cfg);
+        if (e != cudaSuccess || n_clusters < 1) { c->resident_state = -1; cudaGetLastError(); return cudaErrorNotSupported; }
+    }
     e = cudaLaunchKernelEx(&cfg, kern, a);
-    if (e != cudaSuccess) { g_resident_state = -1; cudaGetLastError(); return e; }
-    g_resident_state = 1;
+    if (e != cudaSuccess) { c->resident_state = -1; cudaGetLastError(); return e; }
+    c->resident_state = 1;
     return NSB_LAUNCHED(c, 1);
 }

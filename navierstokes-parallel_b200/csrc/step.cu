@@ -174,13 +174,19 @@ int nsb_ph_sor_begin(nsb_ctx* c) {
 
 static int sor_iterate(nsb_ctx** cs, int n, int max_it, int check) {
     nsb_ctx* c0 = cs[0];
-    const int engine = pick_engine(c0);
-    for (int r = 0; r < n; r++) cs[r]->last_sor_engine = engine;
+    int engine = pick_engine(c0);
     if (engine == NSB_SOR_RESIDENT) {
         CU(c0, cudaSetDevice(c0->device));
-        CU(c0, nsb_launch_sor_resident(c0, max_it, check));
-        return NSB_OK;
+        const cudaError_t e = nsb_launch_sor_resident(c0, max_it, check);
+        if (e == cudaSuccess) { c0->last_sor_engine = engine; return NSB_OK; }
+        // The device refused the cluster / cooperative launch (nothing was enqueued): remember it in this context
+        // and run THIS solve with the streaming sweep instead of failing the step.
+        cudaGetLastError();
+        c0->resident_state = -1;
+        engine = pick_engine(c0);
+        if (engine == NSB_SOR_RESIDENT) return nsb_fail(c0, NSB_ERR_CUDA, "resident SOR launch failed: %s", cudaGetErrorString(e));
     }
+    for (int r = 0; r < n; r++) cs[r]->last_sor_engine = engine;
     if (engine == NSB_SOR_SERIAL_ORDER) {
         CU(c0, cudaSetDevice(c0->device));
         CU(c0, nsb_launch_sor_lex(c0, max_it, check));

@@ -226,3 +226,49 @@ def rows(a: np.ndarray):
     for i in range(n):
         tab[i] = C.cast(base + i * stride, dbl_p)
     return tab
+
+
+# ------------------------------------------------------------------ reference CUDA build (oracle/_ref/librefcuda.so)
+REF_CUDA_LIB_PATH = os.path.join(REF_DIR, "librefcuda.so")
+REF_CUDA_BIN = os.path.join(REF_DIR, "parallel")
+
+
+def have_refcuda() -> bool:
+    return os.path.exists(REF_CUDA_LIB_PATH)
+
+
+_refcuda = None
+
+
+def refcuda():
+    """oracle/ref_cuda_harness.cu: the reference's unmodified src/parallel/main.cu behind two entry points.
+    Needs a GPU to run (its CHECK_CUDA_ERROR exits the process otherwise: call refcuda_device_count first)."""
+    global _refcuda
+    if _refcuda is None:
+        R = C.CDLL(REF_CUDA_LIB_PATH)
+        R.refcuda_device_count.restype = C.c_int
+        R.refcuda_sor.restype = C.c_int
+        R.refcuda_sor.argtypes = [dbl_p, dbl_p, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double,
+                                  C.c_int, C.c_int]
+        R.refcuda_run.restype = C.c_int
+        R.refcuda_run.argtypes = [C.c_int, C.c_double, C.c_int, C.c_int] + [C.c_double] * 9 + \
+                                 [C.c_int, C.c_int, C.c_int, dbl_p, dbl_p, dbl_p, int_p, dbl_p, C.c_int]
+        _refcuda = R
+    return _refcuda
+
+
+def refcuda_sor(p, RHS, dx, dy, omega, eps, max_it, block_size=16):
+    """Reference CUDA SOR (main.cu:656-726) on [i][j] grids; p updated in place; returns it+1 / -1."""
+    ni, nj = p.shape[0] - 2, p.shape[1] - 2
+    return refcuda().refcuda_sor(_ptr(p), _ptr(RHS), ni, nj, dx, dy, omega, eps, max_it, block_size)
+
+
+def refcuda_run(P: Params, block_size=16, max_steps=0, max_log=100000):
+    """Whole run of the reference CUDA solver (main.cu:1046-1103) from zero fields."""
+    u, v, p = zeros(P), zeros(P), zeros(P)
+    ret = (C.c_int * max_log)()
+    dts = (C.c_double * max_log)()
+    n = refcuda().refcuda_run(P.problem, P.f, P.i_max, P.j_max, P.a, P.b, P.T, P.Re, P.g_x, P.g_y, P.tau, P.omega,
+                              P.epsilon, P.max_it, block_size, max_steps, _ptr(u), _ptr(v), _ptr(p), ret, dts, max_log)
+    k = min(n, max_log)
+    return {"steps": n, "u": u, "v": v, "p": p, "sor_ret": list(ret[:k]), "dt": list(dts[:k])}

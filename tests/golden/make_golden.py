@@ -70,6 +70,13 @@ CASES = [
     dict(name="rb_24x40_osc", sor_order=1, params=dict(i_max=24, j_max=40, T=1.2, problem=2, f=3.0, b=1.5)),
     dict(name="rb_33x31", sor_order=1, params=dict(i_max=33, j_max=31, T=0.1, a=1.1, b=0.9, Re=100.0, max_it=300)),
     dict(name="rb_64", sor_order=1, params=dict(i_max=64, j_max=64, T=0.1)),
+    # BASELINE.json configs[0]: the reference's own tests/1.in (256^2, Re 1000, T 0.01, omega 1.7, eps 1e-4, max_it 20000).
+    # SURVEY 4 known answers: serial 20000/20000/17081 sweeps, u_c = -0.0030537512639134965; red-black 3 x 20000,
+    # u_c = -0.0030535551188349812 (asserted below so a regenerated fixture cannot drift from them).
+    dict(name="serial_256_tests1", sor_order=0, params=dict(i_max=256, j_max=256, T=0.01),
+         expect=dict(sor_iters=[20000, 20000, 17081], u_center=-0.0030537512639134965)),
+    dict(name="rb_256_tests1", sor_order=1, params=dict(i_max=256, j_max=256, T=0.01),
+         expect=dict(sor_iters=[20000, 20000, 20000], u_center=-0.0030535551188349812)),
 ]
 
 
@@ -88,6 +95,9 @@ def main():
         else:
             fields = got
             src = "oracle red-black restatement of src/parallel/main.cu:656-726"
+        if "expect" in c:
+            assert [s["sor_iters"] for s in got["log"]] == c["expect"]["sor_iters"], c["name"]
+            assert float(fields["u"][P.i_max // 2, P.j_max // 2]) == c["expect"]["u_center"], c["name"]
         fn = c["name"] + ".npz"
         np.savez_compressed(os.path.join(GOLD, fn), u=fields["u"], v=fields["v"], p=fields["p"])
         ic, jc = P.i_max // 2, P.j_max // 2
