@@ -16,9 +16,10 @@
  *                       maintainer swaps a call site by adding the `nsb_` prefix.
  *
  * Conventions: every function returns 0 on success unless stated; negative = error, text via
- * nsb_last_error().  No exceptions, no global mutable state (the reference's global BLOCK_SIZE,
- * main.cu:26, is not reproduced), one host thread per context, calls are synchronous from the
- * caller's view unless the name ends in _async.  There is NO CPU fallback: without a usable CUDA
+ * nsb_last_error().  No exceptions.  Group A has no global mutable state (the reference's global BLOCK_SIZE,
+ * main.cu:26, is not reproduced); group B keeps ONE cached context per process between calls (so a time loop
+ * does not reallocate; nsb_host_api_reset() drops it) and is therefore, like the reference, single-threaded.
+ * One host thread per context, calls are synchronous from the caller's view.  There is NO CPU fallback: without a usable CUDA
  * device nsb_create fails with NSB_ERR_CUDA.
  */
 #ifndef NSB200_H
@@ -85,7 +86,11 @@ typedef struct nsb_options {
     int sor_chunk_rows;  /* rows per streaming chunk (0 = auto)                                 */
     int sor_check_batch; /* SOR launches the host may run ahead of the device (0 = auto, 24)      */
     void* stream;        /* cudaStream_t to run on (NULL = library creates its own)              */
-    int reserved[8];
+    int sor_pass_k;      /* SOR iterations per pass over HBM of the persistent sweep: 0 / 1 = one, 2 = two
+                            (temporal blocking: half the DRAM traffic, same bits; environment NSB_SOR_K overrides) */
+    int spin_timeout_ms; /* deadline of every in-kernel wait (flags between tasks / slabs); 0 = 2000 ms.  Raise it
+                            under compute-sanitizer or ncu replay, where a kernel runs orders of magnitude slower */
+    int reserved[6];
 } nsb_options;
 
 /* one record per time step: what the reference's loop computes on the host each step */
@@ -213,8 +218,9 @@ int nsb_SOR_iters(double** p, int i_max, int j_max, double delta_x, double delta
 /* integration.h:136 */
 int nsb_FG(double** F, double** G, double** u, double** v, int i_max, int j_max, double Re,
            double g_x, double g_y, double delta_t, double delta_x, double delta_y, double gamma);
-/* io.h:42 */
-double nsb_max_mat(int i_max, int j_max, double** u);
+/* io.h:42 -- for u (i_max+1 rows of j_max+2) and for v (i_max+2 rows of j_max+1, memory.c:15) alike: reads rows
+ * 0..i_max, columns 0..j_max only (what the reference scans, io.c:122-139, plus m[0][0]) */
+double nsb_max_mat(int i_max, int j_max, double** m);
 /* one whole loop body (main.c:88-145) on host grids: uploads u,v,p, runs the step in HBM,
  * downloads u,v,p,F,G,RHS.  The end-to-end call bench.py times. */
 int nsb_timestep(const nsb_params* params, double t, double** u, double** v, double** p,

@@ -52,7 +52,7 @@ class Params(C.Structure):
 class Options(C.Structure):
     _fields_ = [("device", C.c_int), ("div_mode", C.c_int), ("sor_engine", C.c_int),
                 ("sor_chunk_rows", C.c_int), ("sor_check_batch", C.c_int), ("stream", C.c_void_p),
-                ("reserved", C.c_int * 8)]
+                ("sor_pass_k", C.c_int), ("spin_timeout_ms", C.c_int), ("reserved", C.c_int * 6)]
 
 
 class StepInfo(C.Structure):
@@ -186,13 +186,15 @@ class Solver:
     """One simulation resident in HBM (an `nsb_ctx`).  Method names follow the reference."""
 
     def __init__(self, params: Params, device: int = 0, div_mode: int = DIV_AUTO,
-                 sor_engine: int = SOR_AUTO, chunk_rows: int = 0, check_batch: int = 0, stream: int = 0):
+                 sor_engine: int = SOR_AUTO, chunk_rows: int = 0, check_batch: int = 0, stream: int = 0,
+                 pass_k: int = 0, spin_timeout_ms: int = 0):
         self._L = lib()
         self.params = params
         o = Options()
         self._L.nsb_default_options(C.byref(o))
         o.device, o.div_mode, o.sor_engine = device, div_mode, sor_engine
         o.sor_chunk_rows, o.sor_check_batch = chunk_rows, check_batch
+        o.sor_pass_k, o.spin_timeout_ms = pass_k, spin_timeout_ms
         o.stream = stream or None
         h = C.c_void_p()
         rc = self._L.nsb_create(C.byref(params), C.byref(o), C.byref(h))
@@ -326,11 +328,12 @@ def slab_partition(j_max: int, chunk_rows: int, world: int, rank: int):
     return a.value, b.value, c.value, d.value
 
 
-def _options(device, div_mode, sor_engine, chunk_rows, check_batch, stream=0):
+def _options(device, div_mode, sor_engine, chunk_rows, check_batch, stream=0, pass_k=0, spin_timeout_ms=0):
     o = Options()
     lib().nsb_default_options(C.byref(o))
     o.device, o.div_mode, o.sor_engine = device, div_mode, sor_engine
     o.sor_chunk_rows, o.sor_check_batch = chunk_rows, check_batch
+    o.sor_pass_k, o.spin_timeout_ms = pass_k, spin_timeout_ms
     o.stream = stream or None
     return o
 
@@ -339,10 +342,11 @@ class Group:
     """y-slab decomposition driven by ONE process (`nsb_group`): slab k on devices[k].  Equal devices
     are allowed -- the slabs then run in lock step on one stream, which is how a 1-GPU box tests it."""
 
-    def __init__(self, params: Params, devices, div_mode: int = DIV_AUTO, chunk_rows: int = 0, check_batch: int = 0):
+    def __init__(self, params: Params, devices, div_mode: int = DIV_AUTO, chunk_rows: int = 0, check_batch: int = 0,
+                 pass_k: int = 0, spin_timeout_ms: int = 0):
         self._L = lib()
         self.params = params
-        o = _options(0, div_mode, SOR_STREAM, chunk_rows, check_batch)
+        o = _options(0, div_mode, SOR_STREAM, chunk_rows, check_batch, pass_k=pass_k, spin_timeout_ms=spin_timeout_ms)
         dv = (C.c_int * len(devices))(*devices)
         h = C.c_void_p()
         rc = self._L.nsb_group_create(C.byref(params), C.byref(o), len(devices), dv, C.byref(h))
@@ -431,10 +435,10 @@ class SlabSolver(Solver):
     calls step() / run() / SOR() as if it were alone; halos and reductions travel inside the kernels."""
 
     def __init__(self, params: Params, rank: int, world: int, all_gather, device: int = 0, div_mode: int = DIV_AUTO,
-                 chunk_rows: int = 0, check_batch: int = 0):
+                 chunk_rows: int = 0, check_batch: int = 0, pass_k: int = 0, spin_timeout_ms: int = 0):
         self._L = lib()
         self.params = params
-        o = _options(device, div_mode, SOR_STREAM, chunk_rows, check_batch)
+        o = _options(device, div_mode, SOR_STREAM, chunk_rows, check_batch, pass_k=pass_k, spin_timeout_ms=spin_timeout_ms)
         h = C.c_void_p()
         rc = self._L.nsb_create_slab(C.byref(params), C.byref(o), rank, world, C.byref(h))
         if rc != 0:

@@ -84,7 +84,7 @@ extern "C" void nsb_destroy(nsb_ctx* c) {
     for (int r = 0; r < c->world && r < NSB_MAX_RANKS; r++)
         if (r != c->rank && c->peer[r].mapped_ipc && c->peer[r].base) cudaIpcCloseMemHandle(c->peer[r].base);
     if (c->arena) cudaFree(c->arena);
-    double* bufs[] = {c->d_partials, c->d_red_partials, c->d_bandvals, c->d_partials2};
+    double* bufs[] = {c->d_partials, c->d_red_partials, c->d_bandvals, c->d_partials2, c->d_bandvals2};
     if (c->d_claim) cudaFree(c->d_claim);
     if (c->d_done) cudaFree(c->d_done);
     for (double* b : bufs) if (b) cudaFree(b);
@@ -195,7 +195,7 @@ int nsb_create_slab_internal(const nsb_params* P, const nsb_options* opt, int ra
     nsb_sor_plan(c);                                           // chunk_rows, n_strips, n_chunks, n_partials
     if (world == 1) { c->band0 = 0; c->nbands_global = c->n_chunks; }
 
-    // ---- one arena: 8 grids, the sync block, the SOR halo flags, the reduction gather buffer
+    // ---- one arena: 9 grids, the sync block, the SOR halo flags, the reduction gather buffer
     const size_t gbytes = align_up(c->g.elems * sizeof(double), 256);
     size_t off = 0;
     NsbSlabDesc& d = c->desc;
@@ -205,6 +205,7 @@ int nsb_create_slab_internal(const nsb_params* P, const nsb_options* opt, int ra
     d.off_G = off; off += gbytes;
     d.off_p[0] = off; off += gbytes;
     d.off_p[1] = off; off += gbytes;
+    d.off_p2 = off; off += gbytes;
     const size_t off_F = off; off += gbytes;
     d.off_rhs = off; off += gbytes;
     const size_t off_scratch = off; off += gbytes;
@@ -218,10 +219,19 @@ int nsb_create_slab_internal(const nsb_params* P, const nsb_options* opt, int ra
     c->G = (double*)(c->arena + d.off_G); c->F = (double*)(c->arena + off_F);
     c->rhs = (double*)(c->arena + d.off_rhs); c->scratch = (double*)(c->arena + off_scratch);
     c->pbuf[0] = (double*)(c->arena + d.off_p[0]); c->pbuf[1] = (double*)(c->arena + d.off_p[1]);
+    c->pbuf[2] = (double*)(c->arena + d.off_p2);
     c->d_sync = (SlabSync*)(c->arena + d.off_sync);
     c->d_sorflag = (unsigned long long*)(c->arena + d.off_sorflag);
     c->d_gband = (double*)(c->arena + d.off_gband);
     c->pcur = 0;
+    {   // deadline of the in-kernel waits
+        long long ms = c->O.spin_timeout_ms > 0 ? c->O.spin_timeout_ms : 2000;
+        const char* env = getenv("NSB_SPIN_TIMEOUT_MS");
+        if (env && atoll(env) > 0) ms = atoll(env);
+        const unsigned long long ns = (unsigned long long)ms * 1000000ull;
+        CUC(cudaMemcpyAsync(&c->d_sync->timeout_ns, &ns, sizeof ns, cudaMemcpyHostToDevice, c->stream));
+        CUC(cudaStreamSynchronize(c->stream));
+    }
     d.base = (unsigned long long)(uintptr_t)c->arena;
     d.pid = (long long)getpid();
     d.device = c->device; d.rank = rank; d.world = world; d.nj = c->g.nj; d.j_lo = c->j_lo;
@@ -235,17 +245,18 @@ int nsb_create_slab_internal(const nsb_params* P, const nsb_options* opt, int ra
     }
     // this rank seen as a peer of itself
     SlabPeer& me = c->peer[rank];
-    me.base = c->arena; me.u = c->u; me.v = c->v; me.G = c->G; me.rhs = c->rhs; me.p[0] = c->pbuf[0]; me.p[1] = c->pbuf[1];
+    me.base = c->arena; me.u = c->u; me.v = c->v; me.G = c->G; me.rhs = c->rhs; me.p[0] = c->pbuf[0]; me.p[1] = c->pbuf[1]; me.p[2] = c->pbuf[2];
     me.sync = c->d_sync; me.sorflag = c->d_sorflag; me.gband = c->d_gband; me.nj = c->g.nj; me.mapped_ipc = false;
     c->connected = (world == 1);
 
     int np = c->n_partials;
     if (np < 8 * c->g.nj + 64) np = 8 * c->g.nj + 64;
     CUC(cudaMalloc((void**)&c->d_partials, (size_t)np * sizeof(double)));
-    CUC(cudaMalloc((void**)&c->d_partials2, (size_t)2 * c->n_partials * sizeof(double)));
+    CUC(cudaMalloc((void**)&c->d_partials2, (size_t)2 * NSB_SOR_KMAX * c->n_partials * sizeof(double)));
+    CUC(cudaMalloc((void**)&c->d_bandvals2, (size_t)2 * NSB_SOR_KMAX * (c->n_chunks + 1) * sizeof(double)));
     CUC(cudaMalloc((void**)&c->d_claim, 8 * sizeof(unsigned long long)));
     CUC(cudaMalloc((void**)&c->d_done, (size_t)c->n_partials * sizeof(unsigned long long)));
-    CUC(cudaMemsetAsync(c->d_partials2, 0, (size_t)2 * c->n_partials * sizeof(double), c->stream));
+    CUC(cudaMemsetAsync(c->d_partials2, 0, (size_t)2 * NSB_SOR_KMAX * c->n_partials * sizeof(double), c->stream));
     CUC(cudaMemsetAsync(c->d_claim, 0, 8 * sizeof(unsigned long long), c->stream));
     CUC(cudaMemsetAsync(c->d_done, 0, (size_t)c->n_partials * sizeof(unsigned long long), c->stream));
     c->n_red_partials = 3 * 4 * c->g.nj + 64;

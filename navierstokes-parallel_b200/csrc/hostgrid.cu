@@ -3,8 +3,13 @@
 // uploads, runs the CUDA path and downloads the results.  This is the end-to-end path bench.py
 // times (host buffers in, host buffers out).
 //
-// A context is cached per (i_max, j_max, dx, dy, device) so repeated calls from a time loop do not
-// reallocate; nsb_host_api_reset() drops it.  Not thread-safe (the reference is single-threaded).
+// A context is cached per (i_max, j_max, a, b) so repeated calls from a time loop do not reallocate;
+// nsb_host_api_reset() drops it.  This ONE cached context is the only process-global mutable state of the
+// library (group A, the context API, has none); group B is therefore not thread-safe, like the reference
+// (single-threaded, global BLOCK_SIZE main.cu:26).
+// Transfers are stream-ordered: a grid is copied into the scratch grid and transposed on the context's stream,
+// the next transfer queues behind it; the host only waits where it must touch a staging buffer itself and once
+// at the end of a call's downloads.
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -38,6 +43,16 @@ static nsb_ctx* cached_ctx(int i_max, int j_max, double a, double b, const nsb_p
         g_ctx = NULL;
     }
     return g_ctx;
+}
+
+// delta_x, delta_y as the caller passes them (the reference hands them to SOR / FG verbatim), and what follows from them
+static void set_spacing(nsb_ctx* c, double dx, double dy) {
+    c->dx = dx; c->dy = dy;
+    int e1, e2;
+    const double dx2 = dx * dx, dy2 = dy * dy;
+    c->recip_exact = frexp(dx2, &e1) == 0.5 && frexp(dy2, &e2) == 0.5;
+    c->use_recip = (c->O.div_mode == NSB_DIV_RECIP) || (c->O.div_mode == NSB_DIV_AUTO && c->recip_exact);
+    c->rcp_valid = false;
 }
 
 static int ensure_stage(nsb_ctx* c) {
@@ -81,12 +96,12 @@ static int put(nsb_ctx* c, int field, double** m, int nrows, int ncols) {
                              (size_t)ncols * sizeof(double), (size_t)nrows, cudaMemcpyHostToDevice, c->stream));
     } else {
         if (ensure_stage(c)) return NSB_ERR_CUDA;
+        HG(cudaStreamSynchronize(c->stream));                  // an earlier copy may still be reading the staging buffer
         if ((size_t)nrows * (size_t)ncols != total) memset(c->h_stage, 0, total * sizeof(double));
         for (int i = 0; i < nrows; i++) memcpy(c->h_stage + (size_t)i * ld, m[i], (size_t)ncols * sizeof(double));
         HG(cudaMemcpyAsync(c->scratch, c->h_stage, total * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     }
-    HG(nsb_launch_to_xfast(c, c->scratch, dst));
-    HG(cudaStreamSynchronize(c->stream));
+    HG(nsb_launch_to_xfast(c, c->scratch, dst));              // stream-ordered: the next transfer may reuse the scratch grid
     c->red_valid = false;
     return NSB_OK;
 }
@@ -101,13 +116,19 @@ static int get(nsb_ctx* c, int field, double** m, int nrows, int ncols) {
     if (contiguous(m, nrows, ncols)) {
         HG(cudaMemcpy2DAsync(m[0], (size_t)ncols * sizeof(double), c->scratch, ld * sizeof(double),
                              (size_t)ncols * sizeof(double), (size_t)nrows, cudaMemcpyDeviceToHost, c->stream));
-        HG(cudaStreamSynchronize(c->stream));
+        // (no wait here: the callers synchronise once after their last download, get_done)
     } else {
         if (ensure_stage(c)) return NSB_ERR_CUDA;
         HG(cudaMemcpyAsync(c->h_stage, c->scratch, total * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
         HG(cudaStreamSynchronize(c->stream));
         for (int i = 0; i < nrows; i++) memcpy(m[i], c->h_stage + (size_t)i * ld, (size_t)ncols * sizeof(double));
     }
+    return NSB_OK;
+}
+
+static int get_done(nsb_ctx* c) {
+    HG(cudaSetDevice(c->device));
+    HG(cudaStreamSynchronize(c->stream));
     return NSB_OK;
 }
 
@@ -118,13 +139,7 @@ extern "C" int nsb_SOR_iters(double** p, int i_max, int j_max, double delta_x, d
     nsb_ctx* c = cached_ctx(i_max, j_max, delta_x * i_max, delta_y * j_max, NULL);
     if (!c) return NSB_ERR_CUDA;
     // the reference passes delta_x, delta_y themselves: use them verbatim, not a / i_max
-    c->dx = delta_x; c->dy = delta_y;
-    {
-        int e1, e2;
-        const double dx2 = delta_x * delta_x, dy2 = delta_y * delta_y;
-        c->recip_exact = frexp(dx2, &e1) == 0.5 && frexp(dy2, &e2) == 0.5;
-        c->use_recip = (c->O.div_mode == NSB_DIV_RECIP) || (c->O.div_mode == NSB_DIV_AUTO && c->recip_exact);
-    }
+    set_spacing(c, delta_x, delta_y);
     c->P.omega = omega; c->P.epsilon = eps; c->P.max_it = max_it;
     int r;
     if ((r = put(c, NSB_P, p, i_max + 2, j_max + 2))) return r;
@@ -134,6 +149,7 @@ extern "C" int nsb_SOR_iters(double** p, int i_max, int j_max, double delta_x, d
     if (r < 0 && r != NSB_NOT_CONVERGED) return r;
     if (iters) *iters = it;
     int g = get(c, NSB_P, p, i_max + 2, j_max + 2);
+    if (!g) g = get_done(c);
     if (g) return g;
     return r;
 }
@@ -150,13 +166,7 @@ extern "C" int nsb_FG(double** F, double** G, double** u, double** v, int i_max,
                       double g_y, double delta_t, double delta_x, double delta_y, double gamma) {
     nsb_ctx* c = cached_ctx(i_max, j_max, delta_x * i_max, delta_y * j_max, NULL);
     if (!c) return NSB_ERR_CUDA;
-    c->dx = delta_x; c->dy = delta_y;
-    {
-        int e1, e2;
-        const double dx2 = delta_x * delta_x, dy2 = delta_y * delta_y;
-        c->recip_exact = frexp(dx2, &e1) == 0.5 && frexp(dy2, &e2) == 0.5;
-        c->use_recip = (c->O.div_mode == NSB_DIV_RECIP) || (c->O.div_mode == NSB_DIV_AUTO && c->recip_exact);
-    }
+    set_spacing(c, delta_x, delta_y);
     c->P.Re = Re; c->P.g_x = g_x; c->P.g_y = g_y;
     int r;
     if ((r = put(c, NSB_U, u, i_max + 1, j_max + 2))) return r;     // u: rows 0..i_max
@@ -166,16 +176,19 @@ extern "C" int nsb_FG(double** F, double** G, double** u, double** v, int i_max,
     if ((r = nsb_fg(c, delta_t, gamma))) return r;
     if ((r = get(c, NSB_F, F, i_max + 2, j_max + 2))) return r;
     if ((r = get(c, NSB_G, G, i_max + 2, j_max + 2))) return r;
-    return 0;
+    return get_done(c);
 }
 
 // io.h:42
 extern "C" double nsb_max_mat(int i_max, int j_max, double** m) {
     // The reduction kernel yields max u and max v together; here one grid is asked for, so it is
-    // uploaded as u and only that maximum is returned.  All rows 0..i_max are read (u's shape).
+    // uploaded into the u field and only that maximum is returned.  The reference calls max_mat on u
+    // (i_max+1 rows of j_max+2) AND on v (i_max+2 rows of j_max+1, memory.c:15) with the same argument list, and
+    // scans m[0][0] and i = 1..i_max, j = 1..j_max (io.c:122-139): rows 0..i_max, columns 0..j_max are what both
+    // shapes own, so exactly those are read -- nothing past the end of a v row.
     nsb_ctx* c = cached_ctx(i_max, j_max, 1.0, 1.0, NULL);
     if (!c) return NAN;
-    if (put(c, NSB_U, m, i_max + 1, j_max + 2)) return NAN;
+    if (put(c, NSB_U, m, i_max + 1, j_max + 1)) return NAN;
     double um = 0.0, vm = 0.0;
     if (nsb_max_uv(c, &um, &vm)) return NAN;
     return um;
@@ -187,7 +200,7 @@ extern "C" int nsb_timestep(const nsb_params* P, double t, double** u, double** 
     if (!P) return NSB_ERR_ARG;
     nsb_ctx* c = cached_ctx(P->i_max, P->j_max, P->a, P->b, P);
     if (!c) return NSB_ERR_CUDA;
-    c->dx = P->a / P->i_max; c->dy = P->b / P->j_max;
+    set_spacing(c, P->a / P->i_max, P->b / P->j_max);
     const int ni = P->i_max, nj = P->j_max;
     int r;
     if ((r = put(c, NSB_U, u, ni + 1, nj + 2))) return r;
@@ -202,5 +215,5 @@ extern "C" int nsb_timestep(const nsb_params* P, double t, double** u, double** 
     if (F && (r = get(c, NSB_F, F, ni + 2, nj + 2))) return r;
     if (G && (r = get(c, NSB_G, G, ni + 2, nj + 2))) return r;
     if (RHS && (r = get(c, NSB_RHS, RHS, ni + 2, nj + 2))) return r;
-    return NSB_OK;
+    return get_done(c);
 }

@@ -5,10 +5,10 @@
 // COL0 = 3 puts interior column i = 1 on a 32-byte boundary (4 doubles = one "column group", the
 // unit a thread of the streaming kernels owns); pitch is a multiple of 16 doubles (128 B) and
 // leaves >= 4 padding doubles to the right of the ghost column i_max+1, so every group load is in
-// bounds.  ROW0 = 2: two pad rows lie below the ghost row j = 0 and NSB_ROWS_ABOVE = 3 above the
+// bounds.  ROW0 = 4: four pad rows lie below the ghost row j = 0 and NSB_ROWS_ABOVE = 5 above the
 // ghost row j_max+1 (zero-filled, never written), so the streaming SOR kernel, whose row window
-// reaches 3 rows beyond a chunk and which fetches rows in (even, odd) pairs, never needs a bounds
-// test on a load; in a y-slab decomposition the same rows hold the neighbour's halo.  This replaces the reference's row-pointer tables (`double**`, main.cu:103-120)
+// reaches 5 rows beyond a chunk (two iterations per pass, sor_stream.cu) and which fetches rows in (even, odd)
+// pairs, never needs a bounds test on a load; in a y-slab decomposition the same rows hold the neighbour's halo.  This replaces the reference's row-pointer tables (`double**`, main.cu:103-120)
 // and its j-contiguous order, which made every warp access strided.
 #pragma once
 
@@ -19,8 +19,10 @@
 #include "../../include/nsb200.h"
 
 #define NSB_COL0 3
-#define NSB_ROW0 2
-#define NSB_ROWS_ABOVE 3              // pad rows above the ghost row j_max+1
+#define NSB_ROW0 4
+#define NSB_ROWS_ABOVE 5              // pad rows above the ghost row j_max+1
+#define NSB_SOR_KMAX 2                // SOR iterations per pass over HBM of the persistent sweep (temporal blocking)
+#define NSB_HALO_ROWS 5               // p rows a slab keeps of each neighbour: 2 K + 1 for K = NSB_SOR_KMAX
 #define NSB_GROUP 4                 // doubles per column group (32 B)
 #define NSB_STRIP_GROUPS 30         // output groups per warp strip (lanes 1..30; 0 and 31 are halo)
 #define NSB_STRIP_COLS (NSB_STRIP_GROUPS * NSB_GROUP)
@@ -80,8 +82,8 @@ struct StepRed {
 
 // ------------------------------------------------------------------ y-slab decomposition
 // Rank r of `world` owns the global rows j_lo+1 .. j_lo+nj (whole SOR chunks, so every reduction
-// band lies inside one rank).  Local row l is global row j_lo + l.  Local rows 0, -1, -2 and
-// nj+1 .. nj+3 hold the neighbour's rows (halo) where the slab ends inside the domain, and the
+// band lies inside one rank).  Local row l is global row j_lo + l.  Local rows 0 .. -4 and
+// nj+1 .. nj+5 hold the neighbour's rows (halo) where the slab ends inside the domain, and the
 // ghost / pad rows where it ends at a wall.  Everything a peer writes lives in one arena per rank
 // (one IPC handle); peers address it through the offsets of NsbSlabDesc.
 #define NSB_MAX_RANKS 16
@@ -93,7 +95,9 @@ struct SlabSync {                    // in the arena; written by peers with syst
     unsigned long long red_arrived[NSB_MAX_RANKS]; // reduction rounds rank r has contributed to
     int error;                                     // a wait timed out (set locally)
     int pad;
+    unsigned long long timeout_ns;                 // deadline of every in-kernel wait; MUST follow `error` (slab.cuh: spin_timeout_ns)
 };
+static_assert(offsetof(SlabSync, timeout_ns) == offsetof(SlabSync, error) + 8, "SlabSync: timeout_ns must sit 8 bytes behind error");
 
 struct NsbSlabDesc {                 // what a rank tells its peers (POD, travels through IPC / gloo / NCCL)
     unsigned char ipc[64];           // cudaIpcMemHandle_t of the arena
@@ -104,12 +108,13 @@ struct NsbSlabDesc {                 // what a rank tells its peers (POD, travel
     long long off_u, off_v, off_G, off_rhs, off_p[2], off_sync, off_sorflag, off_gband;   // byte offsets in the arena
     long long arena_bytes;
     unsigned char uuid[16];          // cudaDeviceProp::uuid of the owner's GPU
-    unsigned long long reserved[2];
+    long long off_p2;                // third pressure buffer (rotation of the two-iterations-per-pass sweep)
+    unsigned long long reserved[1];
 };
 
 struct SlabPeer {                    // a peer as seen from this rank (device pointers valid HERE)
     unsigned char* base;             // mapped arena
-    double *u, *v, *G, *rhs, *p[2];
+    double *u, *v, *G, *rhs, *p[3];
     SlabSync* sync;
     unsigned long long* sorflag;     // [2][n_strips]: [0] written by ITS lower neighbour, [1] by its upper
     double* gband;                   // [NSB_RED_DEPTH][NSB_RED_Q][nbands_global]
@@ -139,8 +144,8 @@ struct nsb_ctx {
     bool use_recip;        // resolved division mode
     // grids
     double* u; double* v; double* F; double* G; double* rhs;
-    double* pbuf[2];
-    int pcur;              // pbuf[pcur] holds the current pressure
+    double* pbuf[3];       // [2]: third buffer of the persistent sweep's rotation; between solves the pressure is in [0] or [1]
+    int pcur;              // pbuf[pcur] holds the current pressure (0 or 1)
     double* scratch;       // one grid of staging space (layout conversion)
     // slab decomposition (world == 1: the whole domain)
     int rank, world;
@@ -154,7 +159,8 @@ struct nsb_ctx {
     bool connected;
     bool peers_distinct;               // every rank of the decomposition sits on a different physical GPU
     SlabSync* d_sync; unsigned long long* d_sorflag; double* d_gband;
-    unsigned long long seq;            // SOR iterations executed so far (halo flag values)
+    unsigned long long seq;            // SOR halo epochs handed out so far (halo flag values)
+    unsigned long long seq_tail;       // epoch the last pass of the previous persistent launch published
     unsigned long long red_round;      // collective reduction rounds completed so far
     unsigned long long epoch[2];       // halo exchanges pushed to [0] the lower, [1] the upper neighbour
     unsigned long long epoch_in[2];    // halo exchanges expected from [0] the lower, [1] the upper neighbour
@@ -163,7 +169,8 @@ struct nsb_ctx {
     double* d_partials; int n_partials;
     // persistent multi-iteration sweep (sor_stream.cu): claim counter + 4 iteration tickets, one
     // "done" flag per task, double-buffered partials, epoch base of the flags
-    unsigned long long* d_claim; unsigned long long* d_done; double* d_partials2;
+    unsigned long long* d_claim; unsigned long long* d_done; double* d_partials2; double* d_bandvals2;
+    int st_k, st_passes, st_tail, st_buf0;   // what the last persistent solve enqueued (nsb_ph_sor_end settles the buffers)
     unsigned long long flag_base;
     int chunk_rows, n_strips, n_chunks;
     // step reductions
@@ -197,10 +204,12 @@ cudaError_t nsb_launch_reduce_uvp(nsb_ctx* c);     // max u, max v, sum p^2 with
 cudaError_t nsb_launch_sor_begin(nsb_ctx* c);      // threshold from sum p^2, clears the flags
 cudaError_t nsb_launch_sor_stream_iter(nsb_ctx* c, int it, const double* pin, double* pout, int check);
 int nsb_sor_persist_supported(const nsb_ctx* c);
-cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int n_iter, int check);   // all iterations, one launch
+int nsb_sor_pass_k(const nsb_ctx* c);                                    // iterations per pass of the persistent sweep (1 or 2)
+cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int k, int n_pass, int it0, int check, int buf_in, int noclose, int wait_first);
 cudaError_t nsb_launch_sor_lex(nsb_ctx* c, int max_it, int check);       // serial (lexicographic) order, validation
 cudaError_t nsb_launch_sor_simple_iter(nsb_ctx* c, int it, double* p, int check);
 extern "C" int nsb_plan_chunk_rows(int ni, int nj, long long slots, int recip);   // sor_stream.cu, host arithmetic
+extern "C" int nsb_plan_chunk_rows_k(int ni, int nj, long long slots, int recip, int k);
 SorCoef nsb_make_sor_coef(nsb_ctx* c, long long cells);                  // sor_simple.cu; cells = GLOBAL i_max * j_max
 cudaError_t nsb_launch_sor_finish_ghosts(nsb_ctx* c, double* pfinal, const double* pprev);
 cudaError_t nsb_launch_to_xfast(nsb_ctx* c, const double* src_ref, double* dst);   // [i][j] -> grid

@@ -56,9 +56,9 @@ static inline double* row_ptr(double* base, const NsbGrid& g, int l) {
 
 // kind NSB_X_UV: u, v rows 1 -> lower's nj'+1 ; rows nj -> upper's 0          (after the BCs)
 //      NSB_X_G : G row nj -> upper's 0                                          (after F, G)
-//      NSB_X_P : p rows 1..3 -> lower's nj'+1..nj'+3 ; rows nj-2..nj -> upper's -2..0   (SOR entry)
-//      NSB_X_RHS: RHS rows 1..2 -> lower's nj'+1..nj'+2 ; rows nj-1..nj -> upper's -1..0 (after the RHS:
-//                 the fused sweep also updates the two halo rows next to a slab boundary)
+//      NSB_X_P : p rows 1..5 -> lower's nj'+1..nj'+5 ; rows nj-4..nj -> upper's -4..0   (SOR entry; NSB_HALO_ROWS)
+//      NSB_X_RHS: RHS rows 1..4 -> lower's nj'+1..nj'+4 ; rows nj-3..nj -> upper's -3..0 (after the RHS:
+//                 the fused two-iteration sweep also updates the four halo rows next to a slab boundary)
 cudaError_t nsb_launch_halo_push(nsb_ctx* c, int kind) {
     if (c->world == 1) return cudaSuccess;
     if (!c->connected) return cudaErrorNotReady;
@@ -76,10 +76,10 @@ cudaError_t nsb_launch_halo_push(nsb_ctx* c, int kind) {
             dn.cp[1] = {row_ptr(c->v, c->g, 1), row_ptr(d.v, gd, d.nj + 1), 1};
             dn.n = 2;
         } else if (kind == NSB_X_P) {
-            dn.cp[0] = {row_ptr(c->pbuf[pc], c->g, 1), row_ptr(d.p[pc], gd, d.nj + 1), 3};
+            dn.cp[0] = {row_ptr(c->pbuf[pc], c->g, 1), row_ptr(d.p[pc], gd, d.nj + 1), NSB_HALO_ROWS};
             dn.n = 1;
         } else if (kind == NSB_X_RHS) {
-            dn.cp[0] = {row_ptr(c->rhs, c->g, 1), row_ptr(d.rhs, gd, d.nj + 1), 2};
+            dn.cp[0] = {row_ptr(c->rhs, c->g, 1), row_ptr(d.rhs, gd, d.nj + 1), NSB_HALO_ROWS - 1};
             dn.n = 1;
         }
         if (dn.n) { dn.flag = &d.sync->halo_epoch[1]; dn.epoch = ++c->epoch[0]; }   // I am its upper neighbour
@@ -95,10 +95,10 @@ cudaError_t nsb_launch_halo_push(nsb_ctx* c, int kind) {
             up.cp[0] = {row_ptr(c->G, c->g, nj), row_ptr(u.G, gu, 0), 1};
             up.n = 1;
         } else if (kind == NSB_X_P) {
-            up.cp[0] = {row_ptr(c->pbuf[pc], c->g, nj - 2), row_ptr(u.p[pc], gu, -2), 3};
+            up.cp[0] = {row_ptr(c->pbuf[pc], c->g, nj - NSB_HALO_ROWS + 1), row_ptr(u.p[pc], gu, 1 - NSB_HALO_ROWS), NSB_HALO_ROWS};
             up.n = 1;
         } else if (kind == NSB_X_RHS) {
-            up.cp[0] = {row_ptr(c->rhs, c->g, nj - 1), row_ptr(u.rhs, gu, -1), 2};
+            up.cp[0] = {row_ptr(c->rhs, c->g, nj - NSB_HALO_ROWS + 2), row_ptr(u.rhs, gu, 2 - NSB_HALO_ROWS), NSB_HALO_ROWS - 1};
             up.n = 1;
         }
         if (up.n) { up.flag = &u.sync->halo_epoch[0]; up.epoch = ++c->epoch[1]; }   // I am its lower neighbour
@@ -177,7 +177,7 @@ extern "C" int nsb_slab_connect(nsb_ctx* c, const void* descs) {
         }
         p.u = (double*)(p.base + d.off_u); p.v = (double*)(p.base + d.off_v); p.G = (double*)(p.base + d.off_G);
         p.rhs = (double*)(p.base + d.off_rhs);
-        p.p[0] = (double*)(p.base + d.off_p[0]); p.p[1] = (double*)(p.base + d.off_p[1]);
+        p.p[0] = (double*)(p.base + d.off_p[0]); p.p[1] = (double*)(p.base + d.off_p[1]); p.p[2] = (double*)(p.base + d.off_p2);
         p.sync = (SlabSync*)(p.base + d.off_sync);
         p.sorflag = (unsigned long long*)(p.base + d.off_sorflag);
         p.gband = (double*)(p.base + d.off_gband);

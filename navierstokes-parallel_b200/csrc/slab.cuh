@@ -5,7 +5,8 @@
 //   - data crosses GPUs only as plain stores into the neighbour's arena (halo rows, band sums),
 //     issued by the kernel that produced the data, followed by a system-scope release flag;
 //   - a consumer polls its OWN memory (acquire, system scope), never the peer's;
-//   - every wait has a deadline (NSB_SPIN_TIMEOUT_NS) and reports through SlabSync::error instead of
+//   - every wait has a deadline (SlabSync::timeout_ns, 2 s unless nsb_options.spin_timeout_ms / NSB_SPIN_TIMEOUT_MS say
+//     otherwise -- raise it under compute-sanitizer or ncu replay) and reports through SlabSync::error instead of
 //     hanging the device;
 //   - reductions are summed per BAND (one SOR chunk of rows, always inside one rank) and the band
 //     values are combined in an order that depends only on the global band count, so 1, 2, 4 or 8
@@ -15,9 +16,10 @@
 #include "nsb_internal.h"
 #include "nsb_math.cuh"
 
-#ifndef NSB_SPIN_TIMEOUT_NS
-#define NSB_SPIN_TIMEOUT_NS 2000000000ull     // 2 s
-#endif
+// `err` always points at SlabSync::error of this rank; the deadline of the waits sits right behind it
+__device__ __forceinline__ unsigned long long spin_timeout_ns(const int* err) {
+    return *reinterpret_cast<const volatile unsigned long long*>(err + 2);
+}
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
     unsigned long long v;
@@ -39,7 +41,7 @@ __device__ __forceinline__ bool spin_until_ge(const unsigned long long* flag, un
     const unsigned long long t0 = global_timer_ns();
     while (ld_acquire_sys(flag) < want) {
         if (*((volatile int*)err)) return false;             // something already timed out: do not pile up
-        if (global_timer_ns() - t0 > NSB_SPIN_TIMEOUT_NS) {
+        if (global_timer_ns() - t0 > spin_timeout_ns(err)) {
             *((volatile int*)err) = 1;
             return false;
         }

@@ -36,6 +36,7 @@
 //     the comment above it).  Both are instantiated for RECIP (reciprocal product / IEEE division
 //     with the refined reciprocal, nsb_math.cuh) and for MULTI (one slab / several): every body
 //     that is not needed is left out, because the kernel is co-limited by the instruction cache.
+#include <stdlib.h>
 #include <string.h>
 
 #include "nsb_internal.h"
@@ -50,7 +51,7 @@
 #define SOR_MIN_BLOCKS 3
 #endif
 // Steps per unrolled block (= slots of the register window, a compile-time ring) and row-pair stages of the
-// per-warp TMA ring.  SOR_BLK must be a multiple of 2 * SOR_NST and larger than SOR_LAG_RES + 1.
+// per-warp TMA ring.  SOR_BLK must be a multiple of 2 * SOR_NST and at least 3 K + 2 (SorK below).
 #ifndef SOR_BLK
 #define SOR_BLK 8
 #endif
@@ -60,20 +61,29 @@
 #define SOR_USES_PER_BLK (SOR_BLK / 2 / SOR_NST)   // times a stage is filled and read per block
 static_assert(SOR_BLK % (2 * SOR_NST) == 0, "SOR_BLK must be a multiple of 2 * SOR_NST");
 #define SOR_ROW_BYTES 1024     // 32 lanes x 32 B
-#define SOR_ROW_DBL (SOR_ROW_BYTES / 8)
-#define SOR_STAGE_BYTES (4 * SOR_ROW_BYTES)   // p even row, p odd row, RHS even row, RHS odd row
-#define SOR_WARP_SMEM (SOR_NST * SOR_STAGE_BYTES)
-#define SOR_SMEM_BYTES (SOR_WARPS * SOR_WARP_SMEM + SOR_WARPS * 2 * SOR_NST * 8)   // rings + FULL/EMPTY mbarriers
-// Rows behind the arriving row j at which the black update and the residual run (red is always j-1).
-// 2 / 3 is the tightest schedule (each phase uses what the previous one produced in the same step);
-// 3 / 5 makes the three phases of a step independent of each other (more instruction-level
-// parallelism per warp at the price of two more rows in the register window).
-#ifndef SOR_LAG_BLACK
-#define SOR_LAG_BLACK 2
-#endif
-#ifndef SOR_LAG_RES
-#define SOR_LAG_RES 3
-#endif
+// One ring stage = p even row, p odd row, RHS even row, RHS odd row.  With K > 1 sub-iterations per pass a p row
+// carries one more column group on either side of the 32 the lanes own (one more input column is needed there, see
+// sor_colour): 34 groups = 1088 B.
+#define SOR_PROW_BYTES(K) (SOR_ROW_BYTES + ((K) > 1 ? 64 : 0))
+#define SOR_STAGE_BYTES(K) (2 * SOR_PROW_BYTES(K) + 2 * SOR_ROW_BYTES)
+#define SOR_WARP_SMEM(K) (SOR_NST * SOR_STAGE_BYTES(K))
+#define SOR_SMEM_BYTES(K) (SOR_WARPS * SOR_WARP_SMEM(K) + SOR_WARPS * 2 * SOR_NST * 8)   // rings + FULL/EMPTY mbarriers
+// Temporal blocking (K sub-iterations per pass over HBM).  A row that arrived in step j goes through
+//     red (lag 1), black (lag 2), residual (lag 3)        of sub-iteration 0,
+//     red (lag 4), black (lag 5), residual (lag 6)        of sub-iteration 1, ...
+// one phase per step: in step j the phase with lag L works on row j - L.  Phases run in the order of
+// increasing lag inside a step, so a phase finds its north neighbour (lag L-1) already advanced by this
+// step and its south neighbour (lag L+1) not yet -- exactly the state the reference's sequence
+// (ghosts, colour 0, ghosts, colour 1, residual; main.cu:684-706) produces row by row.  K = 2 needs rows
+// j .. j-7 in the window: the 8 slots the unrolled block has anyway.
+template <int K>
+struct SorK {
+    static constexpr int HALO = 2 * K + 1;        // rows a task reads below its first / above its last row; rows pushed across a slab boundary
+    static constexpr int LAG_STORE = 3 * K - 1;   // the last black update: the row is final and is stored
+    static constexpr int LAG_LAST = 3 * K;        // the last residual
+};
+static_assert(SorK<NSB_SOR_KMAX>::LAG_LAST + 2 <= SOR_BLK, "register window too small for the last residual");
+static_assert(SorK<NSB_SOR_KMAX>::HALO <= NSB_ROW0 + 1 && SorK<NSB_SOR_KMAX>::HALO <= NSB_ROWS_ABOVE, "pad rows must cover the task halo");
 
 struct SorStreamArgs {
     const double* __restrict__ pin;
@@ -85,6 +95,7 @@ struct SorStreamArgs {
     int n_groups;            // pitch / 4
     int it, check;
     unsigned int zero;       // always 0; opaque to the compiler
+    int dbg_fixed_loads;     // developer probe (WRONG results): loads never leave two rows, i.e. come from L2 -- the sweep's speed without HBM reads
     SorCoef k;
     double* partials;
     double* bandvals;
@@ -193,7 +204,6 @@ __device__ __forceinline__ void refresh_ghost_columns(double (&X)[4], const Lane
 struct TaskCtx {
     int jstart, jc0, jc1;
     int nj;
-    int rlo, rhi;             // rows that take updates: 1..nj at walls, -1 / nj+2 at a slab boundary
     bool wall_bottom, wall_top;
     bool push_down, push_up;  // this task owns rows of the neighbour's halo
     double* down_col; double* up_col;   // neighbour's pout, this lane's column group, row 0 of its storage
@@ -210,8 +220,11 @@ struct TaskCtx {
     const double* pin_next;   // first row of the next pair to fetch, first column of the strip
     const double* rhs_next;
     int j_next, j_limit;      // pairs whose first row is > j_limit are not fetched
-    uint32_t copy_bytes;      // bytes per row copy (1 KB, clipped at the right edge of the pitch)
+    uint32_t copy_bytes;      // bytes per RHS row copy (1 KB, clipped at the right edge of the pitch)
+    uint32_t copy_bytes_p;    // bytes per p row copy (K > 1: one more group on either side)
+    double ex;                // K > 1: the extra input column of the row that arrived in the previous step (lane 0: west, lane 31: east)
     uint32_t smem_base;       // this warp's ring (shared address)
+    long long ld_step;        // 2 * pitch (0 with the developer probe NSB_DEBUG_FIXED_LOADS: every pair re-reads the same two rows)
 };
 
 // One elected lane arms stage `st` and starts the four copies of the next row pair.  Pairs beyond
@@ -228,6 +241,7 @@ __device__ __forceinline__ bool elect_one() {
     return pred != 0;
 }
 
+template <int K>
 __device__ __forceinline__ void issue_pair(TaskCtx& t, int st, uint32_t empty_phase, bool wait_empty) {
 #ifdef SOR_LANE0_ISSUE
     if (t.lane == 0) {
@@ -237,137 +251,77 @@ __device__ __forceinline__ void issue_pair(TaskCtx& t, int st, uint32_t empty_ph
         const uint32_t bar = t.bar_base + st * 8;
         if (wait_empty) mbar_wait(t.bar_base + (SOR_NST + st) * 8, empty_phase);
         if (t.j_next <= t.j_limit) {
-            const uint32_t dst = t.smem_base + st * SOR_STAGE_BYTES;
-            mbar_expect_tx(bar, 4u * t.copy_bytes);
-            bulk_g2s(dst, t.pin_next, t.copy_bytes, bar);
-            bulk_g2s(dst + SOR_ROW_BYTES, t.pin_next + t.pitch, t.copy_bytes, bar);
-            bulk_g2s(dst + 2 * SOR_ROW_BYTES, t.rhs_next, t.copy_bytes, bar);
-            bulk_g2s(dst + 3 * SOR_ROW_BYTES, t.rhs_next + t.pitch, t.copy_bytes, bar);
+            const uint32_t dst = t.smem_base + st * SOR_STAGE_BYTES(K);
+            mbar_expect_tx(bar, 2u * t.copy_bytes_p + 2u * t.copy_bytes);
+            bulk_g2s(dst, t.pin_next, t.copy_bytes_p, bar);
+            bulk_g2s(dst + SOR_PROW_BYTES(K), t.pin_next + t.pitch, t.copy_bytes_p, bar);
+            bulk_g2s(dst + 2 * SOR_PROW_BYTES(K), t.rhs_next, t.copy_bytes, bar);
+            bulk_g2s(dst + 2 * SOR_PROW_BYTES(K) + SOR_ROW_BYTES, t.rhs_next + t.pitch, t.copy_bytes, bar);
         } else {
             mbar_arrive(bar);
         }
     }
     t.j_next += 2;
-    t.pin_next += 2 * t.pitch;
-    t.rhs_next += 2 * t.pitch;
+    t.pin_next += t.ld_step;
+    t.rhs_next += t.ld_step;
 }
 
-// One pipeline step with compile-time window slot S (row parity == S parity).  sb is the step
-// number of the first step of the current block of 8 (a multiple of 8); the row that arrives in
-// this step is j = jstart + sb + S.
+// ---- one colour phase: sub-iteration Q's red (L = 3Q+1) or black (L = 3Q+2) update of row j - L.
 //   EX: the strip holds ghost / pad columns (first and last strips).
-//   EY: the block of 8 steps touches rows that need gating (walls, chunk ends).
+//   EY: the block of steps touches rows that need gating (walls, chunk ends, pushed rows).
 //   QM: how quotients are formed (nsb_math.cuh); with NSB_QUOT_TRY `ok` is cleared when a quotient that
 //       is USED left the window of the three-operation division (pad / ghost columns of an edge strip may
 //       hold anything and are not counted).
-template <int QM, bool EX, bool EY, int S>
-__device__ __forceinline__ void sor_step(double (&P)[SOR_BLK][4], double (&R)[SOR_BLK][4], const int sb, const uint32_t use0, TaskCtx& t,
-                                         const SorCoef& kf, const LaneGeom& lg, double& acc, bool& ok) {
-    constexpr int LB = SOR_LAG_BLACK, LR = SOR_LAG_RES;
-    constexpr int NS = SOR_BLK;                                                    // window slots
-    static_assert(LR + 2 <= NS, "register window too small for the residual lag");
-    constexpr int sE = S % NS, sD = (S + NS - 1) % NS, sC = (S + NS - 2) % NS;     // rows j, j-1, j-2
-    constexpr int sK = (S + 2 * NS - LB) % NS, sKn = (S + 2 * NS + 1 - LB) % NS, sKs = (S + 2 * NS - 1 - LB) % NS;   // black row, north, south
-    constexpr int sR = (S + 2 * NS - LR) % NS, sRn = (S + 2 * NS + 1 - LR) % NS, sRs = (S + 2 * NS - 1 - LR) % NS;   // residual row, north, south
-    constexpr int st = (S >> 1) % SOR_NST;
-    constexpr int k0 = (S & 1) ? 1 : 0;     // red cells of row j-1: columns k0 and k0 + 2
-    constexpr int k1 = k0 + 2;
-    constexpr int b0 = ((S + LB) & 1) ? 1 : 0;   // black cells of row j-LB
-    constexpr int b1 = b0 + 2;
+// The last black phase (L = 3K-1) leaves the row final and stores it (one full 32-byte sector per lane).
+template <int QM, bool EX, bool EY, int K, int S, int L>
+__device__ __forceinline__ void sor_colour(double (&P)[SOR_BLK][4], double (&R)[SOR_BLK][4], const int j, TaskCtx& t,
+                                           const SorCoef& kf, const LaneGeom& lg, bool& ok) {
+    constexpr int NS = SOR_BLK;
+    constexpr int Q = (L - 1) / 3;
+    constexpr bool BLACK = (L % 3) == 2;
+    constexpr bool STORE = (L == SorK<K>::LAG_STORE);
+    constexpr int HALO = SorK<K>::HALO;
+    constexpr int sX = (S + 2 * NS - L) % NS, sN = (S + 2 * NS - L + 1) % NS, sS = (S + 2 * NS - L - 1) % NS;   // row, north, south
+    // cells of the colour in row j - L: (i + row) % 2 == colour; column k of a lane has i = 1 + k (mod 2), row j has the parity of S
+    constexpr int c0 = ((BLACK ? 1 : 0) + 1 + S + L) & 1;
+    constexpr int c1 = c0 + 2;
+    // rows that take updates: 1 .. nj at walls; beyond a slab boundary sub-iteration Q also advances the
+    // margin rows the later sub-iterations of this pass read
+    constexpr int margin = 1 + 2 * (K - 1 - Q);
     const unsigned FULL = 0xffffffffu;
-    const int j = t.jstart + sb + S;
-
-    // ---- row j (p and RHS) from the ring into registers; after the odd row of a pair the stage
-    //      goes back to the TMA engine
-    {
-        const uint32_t ph = (use0 + (uint32_t)((S >> 1) / SOR_NST)) & 1u;      // use count of the stage, mod 2
-        if ((S & 1) == 0) {
-            mbar_wait(t.bar_base + st * 8, ph ^ t.full_par);
-#ifdef SOR_SYNC_EACH_STEP
-            __syncwarp();
-#endif
+    const int r = j - L;
+    const bool row_in = !EY || ((r >= (t.wall_bottom ? 1 : -margin)) && (r <= (t.wall_top ? t.nj : t.nj + 1 + margin)));
+    double (&X)[4] = P[sX];
+    if (EX) refresh_ghost_columns(X, lg);                               // main.cu:686 / 694
+    if (EY) {
+        if (r == 1 && t.wall_bottom) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) P[sS][k] = X[k];                // p[i][0] = p[i][1]
         }
-        const double2* q = reinterpret_cast<const double2*>(t.lds_lane + st * (SOR_STAGE_BYTES / 8) + (S & 1) * SOR_ROW_DBL);
-        const double2 a = q[0], b = q[1];
-        const double2 c = q[SOR_ROW_BYTES / 8], d = q[SOR_ROW_BYTES / 8 + 1];     // + 2 rows = 2 * 1024 B = 128 double2
-        P[sE][0] = a.x; P[sE][1] = a.y; P[sE][2] = b.x; P[sE][3] = b.y;
-        R[sE][0] = c.x; R[sE][1] = c.y; R[sE][2] = d.x; R[sE][3] = d.y;
-        if (S & 1) {
-            // Both rows of the pair are read: every lane releases the stage on its EMPTY barrier and
-            // the elected lane re-arms the stage only after acquiring that phase (32 arrivals).
-            // The arrive must not overtake the LDS above: neither __syncwarp() nor the arrive's
-            // release semantics kept the bulk copy from overwriting a row whose LDS was still queued
-            // (seen on B200 as sporadically wrong RHS values in the last-loaded 16 bytes).  So the
-            // barrier ADDRESS is made data-dependent on all eight LDS of the pair (this step's
-            // a, b, c, d and the previous step's, now in window slot D): `zero` is a run-time 0 the
-            // compiler cannot fold, and the arrive cannot issue before the loads have landed.
-            const int dep = (__double2hiint(a.x) ^ __double2hiint(b.x) ^ __double2hiint(c.x)) ^
-                            (__double2hiint(d.x) ^ __double2hiint(P[sD][0]) ^ __double2hiint(P[sD][2])) ^
-                            (__double2hiint(R[sD][0]) ^ __double2hiint(R[sD][2]));
-            mbar_arrive(t.bar_base + (SOR_NST + st) * 8 + ((uint32_t)dep & t.zero));
-            issue_pair(t, st, ph ^ t.empty_par, true);
+        if (r == t.nj && t.wall_top) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) P[sN][k] = X[k];                // p[i][j_max+1] = p[i][j_max]
         }
     }
-
-    // ---- colour 0 (red) on row D = j-1; neighbours C (j-2, black cells still old) and E (j)
-    {
-        const int r = j - 1;
-        const bool row_in = !EY || ((r >= t.rlo) && (r <= t.rhi));
-        double (&X)[4] = P[sD];
-        if (EX) refresh_ghost_columns(X, lg);                           // main.cu:686
-        if (EY) {
-            if (r == 1 && t.wall_bottom) {
-#pragma unroll
-                for (int k = 0; k < 4; k++) P[sC][k] = X[k];            // p[i][0] = p[i][1]
-            }
-            if (r == t.nj && t.wall_top) {
-#pragma unroll
-                for (int k = 0; k < 4; k++) P[sE][k] = X[k];            // p[i][j_max+1] = p[i][j_max]
-            }
-        }
-        double xw = 0.0, xe = 0.0;
-        if (k0 == 0) xw = __shfl_up_sync(FULL, X[3], 1);
-        else xe = __shfl_down_sync(FULL, X[0], 1);
-        const double w0 = (k0 == 0) ? xw : X[(k0 + 3) & 3];
-        const double e0 = X[k0 + 1];
-        const double w1 = X[k1 - 1];
-        const double e1 = (k1 == 3) ? xe : X[(k1 + 1) & 3];
-        bool ok0 = true, ok1 = true;
-        const double u0 = sor_cell_q<QM>(X[k0], e0, w0, P[sE][k0], P[sC][k0], R[sD][k0], kf, EX ? ok0 : ok);
-        const double u1 = sor_cell_q<QM>(X[k1], e1, w1, P[sE][k1], P[sC][k1], R[sD][k1], kf, EX ? ok1 : ok);
-        if (row_in && (!EX || lg.inner[k0])) { X[k0] = u0; if (EX) ok = ok && ok0; }
-        if (row_in && (!EX || lg.inner[k1])) { X[k1] = u1; if (EX) ok = ok && ok1; }
+    double xw = 0.0, xe = 0.0;
+    if (c0 == 0) xw = __shfl_up_sync(FULL, X[3], 1);
+    else xe = __shfl_down_sync(FULL, X[0], 1);
+    if (K > 1 && L == 1) {                    // first red update of the pass: the column beyond the halo lanes (sor_step)
+        if (c0 == 0) { if (t.lane == 0) xw = t.ex; }
+        else { if (t.lane == 31) xe = t.ex; }
     }
-
-    // ---- colour 1 (black) on row K = j-LB; neighbours: south (final) and north (red done, black cells still old)
-    {
-        const int r = j - LB;
-        const bool row_in = !EY || ((r >= t.rlo) && (r <= t.rhi));
-        double (&X)[4] = P[sK];
-        if (EX) refresh_ghost_columns(X, lg);                           // main.cu:694
-        if (EY) {
-            if (r == 1 && t.wall_bottom) {
-#pragma unroll
-                for (int k = 0; k < 4; k++) P[sKs][k] = X[k];
-            }
-            if (r == t.nj && t.wall_top) {
-#pragma unroll
-                for (int k = 0; k < 4; k++) P[sKn][k] = X[k];
-            }
-        }
-        double xw = 0.0, xe = 0.0;
-        if (b0 == 0) xw = __shfl_up_sync(FULL, X[3], 1);
-        else xe = __shfl_down_sync(FULL, X[0], 1);
-        const double w0 = (b0 == 0) ? xw : X[(b0 + 3) & 3];
-        const double e0 = X[b0 + 1];
-        const double w1 = X[b1 - 1];
-        const double e1 = (b1 == 3) ? xe : X[(b1 + 1) & 3];
-        bool ok0 = true, ok1 = true;
-        const double u0 = sor_cell_q<QM>(X[b0], e0, w0, P[sKn][b0], P[sKs][b0], R[sK][b0], kf, EX ? ok0 : ok);
-        const double u1 = sor_cell_q<QM>(X[b1], e1, w1, P[sKn][b1], P[sKs][b1], R[sK][b1], kf, EX ? ok1 : ok);
-        if (row_in && (!EX || lg.inner[b0])) { X[b0] = u0; if (EX) ok = ok && ok0; }
-        if (row_in && (!EX || lg.inner[b1])) { X[b1] = u1; if (EX) ok = ok && ok1; }
-        if (EX && (!EY || (r >= t.jc0 && r <= t.jc1))) {
+    const double w0 = (c0 == 0) ? xw : X[(c0 + 3) & 3];
+    const double e0 = X[c0 + 1];
+    const double w1 = X[c1 - 1];
+    const double e1 = (c1 == 3) ? xe : X[(c1 + 1) & 3];
+    bool ok0 = true, ok1 = true;
+    const double u0 = sor_cell_q<QM>(X[c0], e0, w0, P[sN][c0], P[sS][c0], R[sX][c0], kf, EX ? ok0 : ok);
+    const double u1 = sor_cell_q<QM>(X[c1], e1, w1, P[sN][c1], P[sS][c1], R[sX][c1], kf, EX ? ok1 : ok);
+    if (row_in && (!EX || lg.inner[c0])) { X[c0] = u0; if (EX) ok = ok && ok0; }
+    if (row_in && (!EX || lg.inner[c1])) { X[c1] = u1; if (EX) ok = ok && ok1; }
+    if (STORE) {
+        const bool in_chunk = (r >= t.jc0 && r <= t.jc1);     // warp-uniform; the blocks at the ends of a chunk run this body too
+        if (EX && in_chunk) {
             // ghost columns of the final row, as the refresh before colour 1 left them (main.cu:694):
             // the west ghost lives in the halo lane 0 of the first strip, the east ghost in an owner
             // lane (stored below with its group) or in the halo lane 31 of the last strip
@@ -379,32 +333,31 @@ __device__ __forceinline__ void sor_step(double (&P)[SOR_BLK][4], double (&R)[SO
                 else t.pout_row[3] = X[3];
             }
         }
-        // the row is final: store it (one full 32-byte sector per lane)
-        if (lg.owner && (!EY || (r >= t.jc0 && r <= t.jc1))) {
+        if (lg.owner && in_chunk) {
             double2* q = reinterpret_cast<double2*>(t.pout_row);
             q[0] = make_double2(X[0], X[1]);
             q[1] = make_double2(X[2], X[3]);
             if (EY) {
                 // ghost rows j = 0 / j_max+1 as the same refresh left them (copies of row 1 / j_max taken
-                // before the black update, held in the window slots B / D)
+                // before the black update, held in the window slots south / north of the row)
                 if (r == 1 && t.wall_bottom) {
                     double2* h = reinterpret_cast<double2*>(t.pout_row - t.pitch);
-                    h[0] = make_double2(P[sKs][0], P[sKs][1]);
-                    h[1] = make_double2(P[sKs][2], P[sKs][3]);
+                    h[0] = make_double2(P[sS][0], P[sS][1]);
+                    h[1] = make_double2(P[sS][2], P[sS][3]);
                 }
                 if (r == t.nj && t.wall_top) {
                     double2* h = reinterpret_cast<double2*>(t.pout_row + t.pitch);
-                    h[0] = make_double2(P[sKn][0], P[sKn][1]);
-                    h[1] = make_double2(P[sKn][2], P[sKn][3]);
+                    h[0] = make_double2(P[sN][0], P[sN][1]);
+                    h[1] = make_double2(P[sN][2], P[sN][3]);
                 }
-                // y-slab halo: the three rows next to a slab boundary also go straight into the
+                // y-slab halo: the HALO rows next to a slab boundary also go straight into the
                 // neighbour's halo rows over NVLink (peer store), SURVEY 8e
-                if (t.push_down && r <= 3) {
+                if (t.push_down && r <= HALO) {
                     double2* h = reinterpret_cast<double2*>(t.down_col + (long long)(t.down_nj + r + NSB_ROW0) * t.pitch);
                     h[0] = make_double2(X[0], X[1]);
                     h[1] = make_double2(X[2], X[3]);
                 }
-                if (t.push_up && r >= t.nj - 2) {
+                if (t.push_up && r >= t.nj - HALO + 1) {
                     double2* h = reinterpret_cast<double2*>(t.up_col + (long long)(r - t.nj + NSB_ROW0) * t.pitch);
                     h[0] = make_double2(X[0], X[1]);
                     h[1] = make_double2(X[2], X[3]);
@@ -413,74 +366,163 @@ __device__ __forceinline__ void sor_step(double (&P)[SOR_BLK][4], double (&R)[SO
         }
         t.pout_row += t.pitch;
     }
+}
 
-    // ---- residual on row j-LR (final, as are its neighbours) with the ghosts as they are (last refreshed before colour 1)
-    {
-        const int r = j - LR;
-        double (&X)[4] = P[sR];
-        const double xw = __shfl_up_sync(FULL, X[3], 1);
-        const double xe = __shfl_down_sync(FULL, X[0], 1);
-        if (!EY || (r >= t.jc0 && r <= t.jc1)) {   // warp-uniform; rows of the chunk are interior rows
-            double part = 0.0;
+// ---- residual of row j - L (final for its sub-iteration, as are its neighbours) with the ghosts as they are
+//      (last refreshed before colour 1, main.cu:694-702)
+template <int QM, bool EX, bool EY, int S, int L>
+__device__ __forceinline__ void sor_resid(double (&P)[SOR_BLK][4], double (&R)[SOR_BLK][4], const int j, const TaskCtx& t,
+                                          const SorCoef& kf, const LaneGeom& lg, double& acc, bool& ok) {
+    constexpr int NS = SOR_BLK;
+    constexpr int sX = (S + 2 * NS - L) % NS, sN = (S + 2 * NS - L + 1) % NS, sS = (S + 2 * NS - L - 1) % NS;
+    const unsigned FULL = 0xffffffffu;
+    const int r = j - L;
+    double (&X)[4] = P[sX];
+    const double xw = __shfl_up_sync(FULL, X[3], 1);
+    const double xe = __shfl_down_sync(FULL, X[0], 1);
+    if (r >= t.jc0 && r <= t.jc1) {            // warp-uniform; rows of the chunk are interior rows
+        double part = 0.0;
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
-                const double w = (k == 0) ? xw : X[(k + 3) & 3];
-                const double e = (k == 3) ? xe : X[(k + 1) & 3];
-                bool okr = true;
-                const double q = sor_residual_q<QM>(X[k], e, w, P[sRn][k], P[sRs][k], R[sR][k], kf, EX ? okr : ok);
-                if (!EX || lg.inner[k]) { part = fma(q, q, part); if (EX) ok = ok && okr; }
-            }
-            acc += part;                           // non-owner lanes are discarded at the end of the task
+        for (int k = 0; k < 4; k++) {
+            const double w = (k == 0) ? xw : X[(k + 3) & 3];
+            const double e = (k == 3) ? xe : X[(k + 1) & 3];
+            bool okr = true;
+            const double q = sor_residual_q<QM>(X[k], e, w, P[sN][k], P[sS][k], R[sX][k], kf, EX ? okr : ok);
+            if (!EX || lg.inner[k]) { part = fma(q, q, part); if (EX) ok = ok && okr; }
         }
+        acc += part;                           // non-owner lanes are discarded at the end of the task
     }
 }
 
-template <int QM, bool EX, bool EY, int S>
+// the three phases of sub-iteration Q, then those of Q + 1
+template <int QM, bool EX, bool EY, int K, int S, int Q>
+__device__ __forceinline__ void sor_phases(double (&P)[SOR_BLK][4], double (&R)[SOR_BLK][4], const int j, TaskCtx& t,
+                                           const SorCoef& kf, const LaneGeom& lg, double (&acc)[K], bool& ok) {
+    if constexpr (Q < K) {
+        sor_colour<QM, EX, EY, K, S, 3 * Q + 1>(P, R, j, t, kf, lg, ok);
+        sor_colour<QM, EX, EY, K, S, 3 * Q + 2>(P, R, j, t, kf, lg, ok);
+        sor_resid<QM, EX, EY, S, 3 * Q + 3>(P, R, j, t, kf, lg, acc[Q], ok);
+        sor_phases<QM, EX, EY, K, S, Q + 1>(P, R, j, t, kf, lg, acc, ok);
+    }
+}
+
+// One pipeline step with compile-time window slot S (row parity == S parity).  sb is the step
+// number of the first step of the current block of 8 (a multiple of 8); the row that arrives in
+// this step is j = jstart + sb + S.
+template <int QM, bool EX, bool EY, int K, int S>
+__device__ __forceinline__ void sor_step(double (&P)[SOR_BLK][4], double (&R)[SOR_BLK][4], const int sb, const uint32_t use0, TaskCtx& t,
+                                         const SorCoef& kf, const LaneGeom& lg, double (&acc)[K], bool& ok) {
+    constexpr int NS = SOR_BLK;                                                    // window slots
+    constexpr int sE = S % NS, sD = (S + NS - 1) % NS;                             // rows j, j-1
+    constexpr int st = (S >> 1) % SOR_NST;
+    const int j = t.jstart + sb + S;
+
+    // ---- row j (p and RHS) from the ring into registers; after the odd row of a pair the stage
+    //      goes back to the TMA engine
+    double ex_new = 0.0;
+    {
+        const uint32_t ph = (use0 + (uint32_t)((S >> 1) / SOR_NST)) & 1u;      // use count of the stage, mod 2
+        if ((S & 1) == 0) {
+            mbar_wait(t.bar_base + st * 8, ph ^ t.full_par);
+#ifdef SOR_SYNC_EACH_STEP
+            __syncwarp();
+#endif
+        }
+        const double* prow = t.lds_lane + st * (SOR_STAGE_BYTES(K) / 8) + (S & 1) * (SOR_PROW_BYTES(K) / 8);
+        const double* rrow = t.lds_lane + st * (SOR_STAGE_BYTES(K) / 8) + 2 * (SOR_PROW_BYTES(K) / 8) + (S & 1) * (SOR_ROW_BYTES / 8);
+        const double2* q = reinterpret_cast<const double2*>(prow + (K > 1 ? NSB_GROUP : 0));
+        const double2* qr = reinterpret_cast<const double2*>(rrow);
+        const double2 a = q[0], b = q[1];
+        const double2 c = qr[0], d = qr[1];
+        if (K > 1) {
+            // The red update of sub-iteration 0 needs ONE input column beyond the 128 the lanes hold: the west
+            // neighbour of lane 0's column 0 in rows where that cell is red, the east neighbour of lane 31's column 3 in
+            // the others (two sub-iterations and the residual reach 5 columns beyond the 120 owned ones, the halo lanes
+            // hold 4).  It sits in the extra group the bulk copy brought; every lane reads the same word.
+            const double* e = t.lds_lane - t.lane * NSB_GROUP + st * (SOR_STAGE_BYTES(K) / 8) + (S & 1) * (SOR_PROW_BYTES(K) / 8);
+            ex_new = (S & 1) ? e[NSB_GROUP - 1] : e[NSB_GROUP + 32 * NSB_GROUP];
+        }
+        P[sE][0] = a.x; P[sE][1] = a.y; P[sE][2] = b.x; P[sE][3] = b.y;
+        R[sE][0] = c.x; R[sE][1] = c.y; R[sE][2] = d.x; R[sE][3] = d.y;
+        if (S & 1) {
+            // Both rows of the pair are read: every lane releases the stage on its EMPTY barrier and
+            // the elected lane re-arms the stage only after acquiring that phase (32 arrivals).
+            // The arrive must not overtake the LDS above: neither __syncwarp() nor the arrive's
+            // release semantics kept the bulk copy from overwriting a row whose LDS was still queued
+            // (seen on B200 as sporadically wrong RHS values in the last-loaded 16 bytes).  So the
+            // barrier ADDRESS is made data-dependent on all LDS of the pair (this step's
+            // a, b, c, d and the previous step's, now in window slot D): `zero` is a run-time 0 the
+            // compiler cannot fold, and the arrive cannot issue before the loads have landed.
+            int dep = (__double2hiint(a.x) ^ __double2hiint(b.x) ^ __double2hiint(c.x)) ^
+                      (__double2hiint(d.x) ^ __double2hiint(P[sD][0]) ^ __double2hiint(P[sD][2])) ^
+                      (__double2hiint(R[sD][0]) ^ __double2hiint(R[sD][2]));
+            if (K > 1) dep ^= __double2hiint(ex_new) ^ __double2hiint(t.ex);
+            mbar_arrive(t.bar_base + (SOR_NST + st) * 8 + ((uint32_t)dep & t.zero));
+            issue_pair<K>(t, st, ph ^ t.empty_par, true);
+        }
+    }
+    sor_phases<QM, EX, EY, K, S, 0>(P, R, j, t, kf, lg, acc, ok);
+    if (K > 1) t.ex = ex_new;                 // used by the red update of this row in the next step
+}
+
+template <int QM, bool EX, bool EY, int K, int S>
 __device__ __forceinline__ void sor_steps_from(double (&P)[SOR_BLK][4], double (&R)[SOR_BLK][4], const int sb, const uint32_t use0,
-                                               TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, double& acc, bool& ok) {
+                                               TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, double (&acc)[K], bool& ok) {
     if constexpr (S < SOR_BLK) {
-        sor_step<QM, EX, EY, S>(P, R, sb, use0, t, kf, lg, acc, ok);
-        sor_steps_from<QM, EX, EY, S + 1>(P, R, sb, use0, t, kf, lg, acc, ok);
+        sor_step<QM, EX, EY, K, S>(P, R, sb, use0, t, kf, lg, acc, ok);
+        sor_steps_from<QM, EX, EY, K, S + 1>(P, R, sb, use0, t, kf, lg, acc, ok);
     }
 }
 // One unrolled block of SOR_BLK steps; use0 = times every ring stage has been used before this block.
-template <int QM, bool EX, bool EY>
+template <int QM, bool EX, bool EY, int K>
 __device__ __forceinline__ void sor_block8(double (&P)[SOR_BLK][4], double (&R)[SOR_BLK][4], const int sb, const uint32_t use0,
-                                           TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, double& acc, bool& ok) {
-    sor_steps_from<QM, EX, EY, 0>(P, R, sb, use0, t, kf, lg, acc, ok);
+                                           TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, double (&acc)[K], bool& ok) {
+    sor_steps_from<QM, EX, EY, K, 0>(P, R, sb, use0, t, kf, lg, acc, ok);
 }
 
-// Steps of a task: rows jstart .. jc1 + LR arrive (the last ones only to drain the pipeline: the residual of
-// row jc1 runs LR steps after that row arrived; rows above jc1 + 3 are not fetched).
-__device__ __forceinline__ int sor_task_steps(const TaskCtx& t) { return t.jc1 + SOR_LAG_RES - t.jstart + 1; }
+// Steps of a task: rows jstart .. jc1 + 3K arrive (the last ones only to drain the pipeline: the last residual of
+// row jc1 runs 3K steps after that row arrived; rows above jc1 + HALO are not fetched).
+template <int K>
+__device__ __forceinline__ int sor_task_steps(const TaskCtx& t) { return t.jc1 + SorK<K>::LAG_LAST - t.jstart + 1; }
 
-// One task = one strip x one chunk of rows, marched bottom to top by one warp.
-template <int QM, bool EX>
-__device__ __forceinline__ double sor_run_task(TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, bool& ok) {
+// One task = one strip x one chunk of rows, marched bottom to top by one warp.  acc[q] = this lane's share of
+// sum r^2 of sub-iteration q over the rows of the chunk.
+template <int QM, bool EX, int K>
+__device__ __forceinline__ void sor_run_task(TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, double (&acc)[K], bool& ok) {
     double P[SOR_BLK][4], R[SOR_BLK][4];
 #pragma unroll
     for (int s = 0; s < SOR_BLK; s++)
 #pragma unroll
         for (int k = 0; k < 4; k++) { P[s][k] = 0.0; R[s][k] = 0.0; }
-    double acc = 0.0;
-    const int n_steps = sor_task_steps(t);
+#pragma unroll
+    for (int q = 0; q < K; q++) acc[q] = 0.0;
+    const int n_steps = sor_task_steps<K>(t);
     uint32_t use0 = 0u;
     for (int sb = 0; sb < n_steps; sb += SOR_BLK, use0 += SOR_USES_PER_BLK) {
         const int jb = t.jstart + sb;                        // row arriving in the first step of the block
-        // rows touched by the block (B = SOR_BLK): residual jb-LR .. jb+B-1-LR, stores jb-LB .. jb+B-1-LB, loads jb .. jb+B-1
+        // rows touched by the block (B = SOR_BLK): residuals jb-3K .. jb+B-4, stores jb-(3K-1) .. jb+B-3K, updates up to jb+B-2, loads jb .. jb+B-1
 #ifdef SOR_NO_LEAN
         const bool clean = false;
 #else
-        const bool clean = (jb - SOR_LAG_RES >= t.jc0) && (jb + SOR_BLK - 1 - SOR_LAG_BLACK <= t.jc1) && (jb + SOR_BLK - 1 <= t.nj) &&
-                           !(t.push_down && jb - SOR_LAG_BLACK <= 3) && !(t.push_up && jb + SOR_BLK - 1 - SOR_LAG_BLACK >= t.nj - 2);
+        // The plain body gates nothing but the stores and the residual rows (by the rows of the chunk): it serves every
+        // block whose updates stay off the wall rows 1 / nj (ghost-row mirrors, rows that must not change) and whose
+        // stores are not pushed to a neighbouring slab -- i.e. all blocks of all chunks but the first and the last one.
+        // (r1: a separate chunk-edge body made the kernel larger and slower; the gates cost ~3 % of the plain body's
+        // instructions and keep the edge blocks of short chunks out of the 2.5 x larger wall body.)
+        constexpr int LS = SorK<K>::LAG_STORE, HALO = SorK<K>::HALO;
+        const bool clean = (!t.wall_bottom || jb - LS >= 2) && (!t.wall_top || jb + SOR_BLK - 2 <= t.nj - 1) &&
+                           !(t.push_down && jb - LS <= HALO) && !(t.push_up && jb + SOR_BLK - 1 - LS >= t.nj - HALO + 1);
 #endif
         // (a fourth variant <EX, !EY> for the interior rows of the two edge strips was measured: the larger
         //  kernel body costs the LEAN path 10 % -- 5.27 against 5.86 TB/s at 8192^2 -- and was dropped)
-        if (EX) sor_block8<QM, true, true>(P, R, sb, use0, t, kf, lg, acc, ok);
-        else if (clean && QM != NSB_QUOT_FULL) sor_block8<QM, false, false>(P, R, sb, use0, t, kf, lg, acc, ok);
-        else sor_block8<QM, false, true>(P, R, sb, use0, t, kf, lg, acc, ok);
+        if (EX) sor_block8<QM, true, true, K>(P, R, sb, use0, t, kf, lg, acc, ok);
+        else if (clean && QM != NSB_QUOT_FULL) sor_block8<QM, false, false, K>(P, R, sb, use0, t, kf, lg, acc, ok);
+        else sor_block8<QM, false, true, K>(P, R, sb, use0, t, kf, lg, acc, ok);
     }
-    return lg.owner ? acc : 0.0;
+    if (!lg.owner) {
+#pragma unroll
+        for (int q = 0; q < K; q++) acc[q] = 0.0;
+    }
 }
 
 // Phase parities of a warp's mbarriers after one task of n_steps rows (see sor_persist_kernel).
@@ -494,22 +536,20 @@ __device__ __forceinline__ void sor_advance_parities(int n_steps, uint32_t& full
 // first pass uses the three-operation quotients; if any lane saw an operand outside their window
 // (non-finite or denormal-range data) the SAME task runs again with out-of-line divisions -- its
 // outputs (rows, halo rows, partial) are simply written twice, nothing is published in between.
-// `row0` = &array[row jstart][first column of the strip] offsets, as set up by the caller.
-template <bool RECIP>
-__device__ __forceinline__ double sor_task(TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, bool edge_strip,
-                                           uint32_t& full_par, uint32_t& empty_par) {
+template <bool RECIP, int K>
+__device__ __forceinline__ void sor_task(TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, bool edge_strip,
+                                         uint32_t& full_par, uint32_t& empty_par, double (&acc)[K]) {
     constexpr int QM = RECIP ? NSB_QUOT_RECIP : NSB_QUOT_TRY;
-    const int n_steps = sor_task_steps(t);
+    const int n_steps = sor_task_steps<K>(t);
     const double* pin0 = t.pin_next; const double* rhs0 = t.rhs_next; double* pout0 = t.pout_row;
     t.full_par = full_par; t.empty_par = empty_par;
     sor_advance_parities(n_steps, full_par, empty_par);
     __syncwarp();
 #pragma unroll
-    for (int q = 0; q < SOR_NST; q++) issue_pair(t, q, 0u, false);
+    for (int q = 0; q < SOR_NST; q++) issue_pair<K>(t, q, 0u, false);
     bool ok = true;
-    double acc;
-    if (edge_strip) acc = sor_run_task<QM, true>(t, kf, lg, ok);
-    else acc = sor_run_task<QM, false>(t, kf, lg, ok);
+    if (edge_strip) sor_run_task<QM, true, K>(t, kf, lg, acc, ok);
+    else sor_run_task<QM, false, K>(t, kf, lg, acc, ok);
     if (!RECIP) {
         if (!__all_sync(0xffffffffu, ok)) {
             t.pin_next = pin0; t.rhs_next = rhs0; t.pout_row = pout0; t.j_next = t.jstart;
@@ -517,18 +557,81 @@ __device__ __forceinline__ double sor_task(TaskCtx& t, const SorCoef& kf, const 
             sor_advance_parities(n_steps, full_par, empty_par);
             __syncwarp();
 #pragma unroll
-            for (int q = 0; q < SOR_NST; q++) issue_pair(t, q, 0u, false);
-            if (edge_strip) acc = sor_run_task<NSB_QUOT_FULL, true>(t, kf, lg, ok);
-            else acc = sor_run_task<NSB_QUOT_FULL, false>(t, kf, lg, ok);
+            for (int q = 0; q < SOR_NST; q++) issue_pair<K>(t, q, 0u, false);
+            if (edge_strip) sor_run_task<NSB_QUOT_FULL, true, K>(t, kf, lg, acc, ok);
+            else sor_run_task<NSB_QUOT_FULL, false, K>(t, kf, lg, acc, ok);
         }
     }
-    return acc;
+}
+
+// Geometry of one task (strip, chunk) for a pass of K sub-iterations: everything of TaskCtx that does not depend on
+// the buffers.  MULTI: several y-slabs.
+template <bool MULTI, int K>
+__device__ __forceinline__ void sor_task_geometry(TaskCtx& t, LaneGeom& lg, bool& edge_strip, const SorStreamArgs& a,
+                                                  int strip, int chunk, int lane) {
+    constexpr int HALO = SorK<K>::HALO;
+    const unsigned FULLM = 0xffffffffu;
+    const int g0 = strip * NSB_STRIP_GROUPS;             // first column group of the strip
+    const int g = g0 + lane;                             // column group of this lane
+    const int i0 = g * NSB_GROUP - NSB_COL0;             // i of column k = 0
+    bool all_inner = (g < a.n_groups);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        lg.inner[k] = (i0 + k >= 1) && (i0 + k <= a.ni);
+        all_inner = all_inner && lg.inner[k];
+    }
+    lg.owner = (g < a.n_groups) && lane >= 1 && lane <= NSB_STRIP_GROUPS;
+    lg.ghostW = (i0 + 3 == 0);
+    const int kg = a.ni + 1 - i0;
+    lg.kGhostE = (kg >= 0 && kg <= 3) ? kg : -1;
+    lg.warpW = __any_sync(FULLM, lg.ghostW);
+    lg.warpE = __any_sync(FULLM, lg.kGhostE >= 0);
+#ifdef SOR_FORCE_EX
+    edge_strip = true;
+#else
+    edge_strip = !__all_sync(FULLM, all_inner);
+#endif
+    t.jc0 = 1 + chunk * a.chunk_rows;
+    t.jc1 = min(t.jc0 + a.chunk_rows - 1, a.nj);
+    t.jstart = t.jc0 - HALO;                             // even, because chunk_rows is even and HALO is odd
+    t.nj = a.nj;
+    t.wall_bottom = !(MULTI && (a.wall_bottom == 0)); t.wall_top = !(MULTI && (a.wall_top == 0));
+    t.push_down = (MULTI && (!t.wall_bottom && t.jc0 <= HALO));
+    t.push_up = (MULTI && (!t.wall_top && t.jc1 >= a.nj - HALO + 1));
+    t.pitch = a.pitch;
+    t.ld_step = a.dbg_fixed_loads ? 0 : 2 * a.pitch;
+    t.lane = lane;
+    t.zero = a.zero;
+    t.j_next = t.jstart;
+    t.j_limit = min(t.jc1 + HALO, a.nj + HALO);
+    t.down_nj = a.down_nj;
+    const int groups_here = min(32, a.n_groups - g0);
+    t.copy_bytes = (uint32_t)groups_here * 32u;
+    t.copy_bytes_p = K > 1 ? (uint32_t)min(34, a.n_groups - g0 + 1) * 32u : t.copy_bytes;   // from group g0 - 1
+    t.ex = 0.0;
+}
+
+// Buffers of a task: first rows to fetch, first row to store, the neighbours' halo rows.
+template <int K>
+__device__ __forceinline__ void sor_task_buffers(TaskCtx& t, const double* pin, double* pout, const double* rhs,
+                                                 double* down_pout, double* up_pout, int strip, int lane) {
+    const long long coff = (long long)strip * NSB_STRIP_GROUPS * NSB_GROUP;    // first column of the strip
+    const long long row_first = (long long)(t.jstart + NSB_ROW0) * t.pitch;
+    t.pin_next = pin + row_first + coff - (K > 1 ? NSB_GROUP : 0);     // K > 1: the copy starts one group to the left
+    t.rhs_next = rhs + row_first + coff;
+    t.pout_row = pout + row_first - SorK<K>::LAG_STORE * t.pitch + coff + (long long)lane * NSB_GROUP;
+    t.down_col = down_pout + coff + (long long)lane * NSB_GROUP;
+    t.up_col = up_pout + coff + (long long)lane * NSB_GROUP;
 }
 
 #ifdef SOR_MAXNREG
 #define SOR_KERNEL_ATTR __maxnreg__(SOR_MAXNREG)
 #else
 #define SOR_KERNEL_ATTR __launch_bounds__(SOR_THREADS, SOR_MIN_BLOCKS)
+#endif
+// K = 2 keeps 8 rows of p and 7 of RHS in registers (~230): two blocks per SM
+#ifndef SOR_MIN_BLOCKS_K2
+#define SOR_MIN_BLOCKS_K2 2
 #endif
 // MULTI: several y-slabs (world > 1).  The single-slab instantiation carries no halo pushes, peer flags or slab
 // reductions: a smaller body, which the instruction cache rewards (8192^2 265 -> 257 us, 2048^2 45.7 -> 39.6 us).
@@ -548,58 +651,16 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
             // slab boundaries first: their rows reach the neighbours a whole launch before they are read
             chunk = (chunk == 0) ? 0 : (chunk == 1) ? a.n_chunks - 1 : chunk - 1;
         }
-        const int g0 = strip * NSB_STRIP_GROUPS;             // first column group of the strip
-        const int g = g0 + lane;                             // column group of this lane
-        const int i0 = g * NSB_GROUP - NSB_COL0;             // i of column k = 0
         LaneGeom lg;
-        bool all_inner = (g < a.n_groups);
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            lg.inner[k] = (i0 + k >= 1) && (i0 + k <= a.ni);
-            all_inner = all_inner && lg.inner[k];
-        }
-        lg.owner = (g < a.n_groups) && lane >= 1 && lane <= NSB_STRIP_GROUPS;
-        lg.ghostW = (i0 + 3 == 0);
-        const int kg = a.ni + 1 - i0;
-        lg.kGhostE = (kg >= 0 && kg <= 3) ? kg : -1;
-        lg.warpW = __any_sync(0xffffffffu, lg.ghostW);
-        lg.warpE = __any_sync(0xffffffffu, lg.kGhostE >= 0);
-#ifdef SOR_FORCE_EX
-        const bool edge_strip = true;
-#else
-        const bool edge_strip = !__all_sync(0xffffffffu, all_inner);
-#endif
-
         TaskCtx t;
-        t.jc0 = 1 + chunk * a.chunk_rows;
-        t.jc1 = min(t.jc0 + a.chunk_rows - 1, a.nj);
-        t.jstart = t.jc0 - 3;                                // even, because chunk_rows is even
-        t.nj = a.nj;
-        t.wall_bottom = !(MULTI && (a.wall_bottom == 0)); t.wall_top = !(MULTI && (a.wall_top == 0));
-        t.rlo = t.wall_bottom ? 1 : -1;
-        t.rhi = t.wall_top ? a.nj : a.nj + 2;
-        t.push_down = (MULTI && (!t.wall_bottom && t.jc0 <= 3));
-        t.push_up = (MULTI && (!t.wall_top && t.jc1 >= a.nj - 2));
-        t.pitch = a.pitch;
-        t.lane = lane;
-        t.zero = a.zero;
+        bool edge_strip;
+        sor_task_geometry<MULTI, 1>(t, lg, edge_strip, a, strip, chunk, lane);
         t.full_par = 0u; t.empty_par = 0u;
-        const long long coff = (long long)g0 * NSB_GROUP;    // first column of the strip
-        const long long row_first = (long long)(t.jstart + NSB_ROW0) * a.pitch;
-        t.pin_next = a.pin + row_first + coff;
-        t.rhs_next = a.rhs + row_first + coff;
-        t.j_next = t.jstart;
-        t.j_limit = min(t.jc1 + 3, a.nj + 3);
-        t.pout_row = a.pout + row_first - SOR_LAG_BLACK * a.pitch + coff + (long long)lane * NSB_GROUP;
-        t.down_col = a.down_pout + coff + (long long)lane * NSB_GROUP;
-        t.up_col = a.up_pout + coff + (long long)lane * NSB_GROUP;
-        t.down_nj = a.down_nj;
-        const int groups_here = min(32, a.n_groups - g0);
-        t.copy_bytes = (uint32_t)groups_here * 32u;
-        unsigned char* ring = smem_raw + warp * SOR_WARP_SMEM;
+        sor_task_buffers<1>(t, a.pin, a.pout, a.rhs, a.down_pout, a.up_pout, strip, lane);
+        unsigned char* ring = smem_raw + warp * SOR_WARP_SMEM(1);
         t.lds_lane = reinterpret_cast<const double*>(ring) + lane * NSB_GROUP;
         t.smem_base = smem_u32(ring);
-        t.bar_base = smem_u32(smem_raw + SOR_WARPS * SOR_WARP_SMEM + warp * 2 * SOR_NST * 8);
+        t.bar_base = smem_u32(smem_raw + SOR_WARPS * SOR_WARP_SMEM(1) + warp * 2 * SOR_NST * 8);
 
         // ---- y-slab: the halo rows this task reads were stored by the neighbour's launch seq-1
         if ((MULTI && (a.world > 1)) && a.it > 0) {    // it == 0: the halo came with the p exchange at the solve entry
@@ -626,8 +687,9 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         }
         uint32_t full_par = 0u, empty_par = 0u;
-        double acc = sor_task<RECIP>(t, a.k, lg, edge_strip, full_par, empty_par);
-        acc = warp_sum(acc);
+        double accs[1];
+        sor_task<RECIP, 1>(t, a.k, lg, edge_strip, full_par, empty_par, accs);
+        const double acc = warp_sum(accs[0]);
         if (lane == 0) a.partials[chunk * a.n_strips + strip] = acc;
 
         if (t.push_down || t.push_up) {                      // halo rows are out: tell the neighbour(s)
@@ -667,35 +729,42 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
 }
 
 // ------------------------------------------------------------------------------------------
-// Persistent multi-iteration sweep (single slab): ALL iterations of a solve in one launch.
+// Persistent multi-iteration sweep: ALL iterations of a solve in one launch, K sub-iterations per pass over HBM.
 //
-// Why: one launch per iteration costs a pipeline drain per iteration -- a task (one warp marching up
+// Why persistent: one launch per iteration costs a pipeline drain per iteration -- a task (one warp marching up
 // 126 rows) lives ~100-150 us, so the last round of blocks leaves most SMs idle; measured launch time
 // = 75 us + 4.03 us per 120-row band at 8192 columns (profiles/r1d_wave_probe.txt), i.e. 22 % of a
 // launch at 8192^2 is drain.  Here the warps of a fixed grid claim tasks from one global counter,
-// task id = iteration * n_tasks + (chunk * n_strips + strip), and a task of iteration n starts as
-// soon as its 3 x 3 neighbourhood of tasks of iteration n-1 is done (their rows are what it reads,
-// and they are the only readers of the rows it overwrites in the ping-pong buffer), so the sweep
-// of iteration n+1 follows the sweep of iteration n up the grid without a global barrier.
+// task id = pass * n_tasks + (chunk * n_strips + strip), and a task of pass n starts as
+// soon as its 3 x 3 neighbourhood of tasks of pass n-1 is done (their rows are what it reads,
+// and together with THEIR 3 x 3 neighbourhoods of pass n-2 they are the only readers of the rows it
+// overwrites), so the sweep of pass n+1 follows the sweep of pass n up the grid without a global barrier.
+// Why K = 2 (temporal blocking, north_star): the pass reads p and RHS once and writes p once for TWO
+// iterations -- 12 B per cell-update instead of 24 -- at the price of 5 + 5 halo rows per chunk instead of 3 + 3.
+//   - buffers: three pressure buffers in rotation (pass n reads buffer n mod 3 and writes n+1 mod 3), so the
+//     input of pass n is still intact when pass n is closed: if its FIRST sub-iteration met the threshold, the
+//     host replays that single iteration from the intact input (K = 1 launch, bit-identical);
 //   - deadlock freedom: ids are claimed in order and a task only waits for smaller ids, which are
 //     running on resident warps or finished; every wait still has a deadline (slab.cuh);
-//   - residual: per-task partials (double-buffered by iteration parity), the warp that takes the
-//     last ticket of an iteration sums them in the same fixed order as the one-launch-per-iteration
-//     kernel (same bits), closes the iteration and publishes the control block;
-//   - convergence: a task of iteration n waits until iteration n-2 is closed and stops if that or an
-//     earlier one converged.  Tasks of iteration m+1 may run after iteration m converged: they write
-//     the OTHER ping-pong buffer, the converged iterate stays intact (same contract as the queued
-//     launches of the per-iteration kernel).
+//   - residual: per-task partials per sub-iteration (double-buffered by pass parity), the warp that takes the
+//     last ticket of a pass sums them in the same fixed order as the one-launch-per-iteration
+//     kernel (same bits) and closes the K iterations in order, stopping at the first that converged;
+//   - convergence: a task of pass n waits until pass n-2 is closed and stops if that or an
+//     earlier one converged.  Tasks of pass m+1 may run after pass m converged: they write
+//     a buffer that neither holds the converged iterate nor the input of pass m.
 struct SorPersistArgs {
-    SorStreamArgs s;                 // geometry, coefficients, ctl; pin / pout = buffers of iteration 0
-    int n_iter;
-    unsigned long long* claim;       // [0] task counter, [1..4] tickets of iterations mod 4
-    unsigned long long* done;        // [n_tasks] epoch of the last iteration the task finished
-    unsigned long long flag_base;    // epoch of "before iteration 0 of this launch"
-    double* partials2;               // [2][n_tasks]
-    // y-slabs: this rank's two pressure buffers and the neighbours' (index = buffer number), the buffer
-    // iteration 0 reads, and the reduction round of iteration 0
-    double* own_p[2]; double* down_p[2]; double* up_p[2];
+    SorStreamArgs s;                 // geometry, coefficients, ctl; s.it = global number of the first iteration of this launch
+    int n_pass;                      // passes of K iterations each
+    int noclose;                     // replay of an iteration that is already closed: do not close again
+    int wait_first;                  // y-slabs: pass 0 reads halo rows pushed by the previous launch (epoch s.seq)
+    unsigned long long* claim;       // [0] task counter, [1..4] tickets of passes mod 4
+    unsigned long long* done;        // [n_tasks] epoch of the last pass the task finished
+    unsigned long long flag_base;    // epoch of "before pass 0 of this launch"
+    double* partials2;               // [2][NSB_SOR_KMAX][n_tasks]
+    double* bandvals2;               // [2][NSB_SOR_KMAX][n_chunks + 1]
+    // this rank's three pressure buffers and the neighbours' (index = buffer number), the buffer
+    // pass 0 reads, and the reduction round of iteration s.it
+    double* own_p[3]; double* down_p[3]; double* up_p[3];
     int buf0;
     unsigned long long round0;
 };
@@ -719,21 +788,47 @@ __device__ __forceinline__ bool spin_gpu_ge(const unsigned long long* flag, unsi
     const unsigned long long t0 = global_timer_ns();
     while (ld_acquire_gpu(flag) < want) {
         if (*((volatile int*)err)) return false;
-        if (global_timer_ns() - t0 > NSB_SPIN_TIMEOUT_NS) { *((volatile int*)err) = 1; return false; }
+        if (global_timer_ns() - t0 > spin_timeout_ns(err)) { *((volatile int*)err) = 1; return false; }
         __nanosleep(64);
     }
     return true;
 }
 
-template <bool RECIP, bool MULTI>
-__global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
+// Band sums of one sub-iteration's partials (one band = one chunk of rows, strips in a fixed order), by one warp.
+// 16 bands at a time, so that 16 loads per lane are in flight: one band after the other
+// (an L2 round trip each) took ~0.5 us per band, 40 us for the 86 bands of 2048^2 -- as long as
+// the iteration itself, and iteration n+2 waits for this closing (ncu source page, 2048^2:
+// half of all warp samples sat in the `iters` poll).  Per band the additions are those
+// of warp_ordered_sum (lane-strided partials in q order, then the butterfly): same bits.
+__device__ __forceinline__ void sor_band_sums(const double* part, double* bandvals, int n_chunks, int n_strips, int lane) {
+    for (int b0 = 0; b0 < n_chunks; b0 += 16) {
+        double sb[16];
+#pragma unroll
+        for (int u = 0; u < 16; u++) sb[u] = 0.0;
+        for (int q = lane; q < n_strips; q += 32) {
+#pragma unroll
+            for (int u = 0; u < 16; u++)
+                if (b0 + u < n_chunks) sb[u] += __ldcg(part + (size_t)(b0 + u) * n_strips + q);
+        }
+#pragma unroll
+        for (int u = 0; u < 16; u++) sb[u] = warp_sum(sb[u]);
+        if (lane == 0) {
+#pragma unroll
+            for (int u = 0; u < 16; u++)
+                if (b0 + u < n_chunks) bandvals[b0 + u] = sb[u];
+        }
+    }
+}
+
+template <bool RECIP, bool MULTI, int K>
+__global__ void __launch_bounds__(SOR_THREADS, (K == 1 ? SOR_MIN_BLOCKS : SOR_MIN_BLOCKS_K2)) sor_persist_kernel(const SorPersistArgs pa) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const SorStreamArgs& a = pa.s;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned FULLM = 0xffffffffu;
-    const unsigned long long total = (unsigned long long)pa.n_iter * (unsigned long long)a.n_tasks;
-    unsigned char* ring = smem_raw + warp * SOR_WARP_SMEM;
-    const uint32_t bar_base = smem_u32(smem_raw + SOR_WARPS * SOR_WARP_SMEM + warp * 2 * SOR_NST * 8);
+    const unsigned long long total = (unsigned long long)pa.n_pass * (unsigned long long)a.n_tasks;
+    unsigned char* ring = smem_raw + warp * SOR_WARP_SMEM(K);
+    const uint32_t bar_base = smem_u32(smem_raw + SOR_WARPS * SOR_WARP_SMEM(K) + warp * 2 * SOR_NST * 8);
     // The mbarriers are initialised once and live across the tasks of this warp.  Per task and stage
     // the FULL barrier completes (pairs per stage + 1) phases (the last re-arm is never waited for, it
     // is a plain arrive), the EMPTY barrier (pairs per stage): the parities a task starts with follow.
@@ -751,16 +846,17 @@ __global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
         if (lane == 0) id = atomicAdd(pa.claim, 1ull);
         id = __shfl_sync(FULLM, id, 0);
         if (id >= total) break;
-        const int it = (int)(id / (unsigned long long)a.n_tasks);
-        const int task = (int)(id - (unsigned long long)it * (unsigned long long)a.n_tasks);
+        const int ps = (int)(id / (unsigned long long)a.n_tasks);                 // pass
+        const int task = (int)(id - (unsigned long long)ps * (unsigned long long)a.n_tasks);
+        const int it_first = a.it + ps * K;                                        // global number of this pass's first iteration
         const int strip = task % a.n_strips;
         int chunk = task / a.n_strips;
         if ((MULTI && (a.world > 1)) && a.n_chunks > 1)     // slab boundaries first: their rows travel while the interior is swept
             chunk = (chunk == 0) ? 0 : (chunk == 1) ? a.n_chunks - 1 : chunk - 1;
-        const int tslot = chunk * a.n_strips + strip;      // index of this task's flag and partial
+        const int tslot = chunk * a.n_strips + strip;      // index of this task's flag and partials
 
-        // ---- may this iteration run?  iteration it-2 must be closed, and nothing before may have converged
-        // (the wait also keeps the double-buffered partials and the 4 tickets of iteration it-2 / it-4 safe,
+        // ---- may this pass run?  pass ps-2 must be closed, and nothing before may have converged
+        // (the wait also keeps the double-buffered partials and the 4 tickets of pass ps-2 / ps-4 safe,
         //  so it does not depend on `check`)
         int stop = 0;
         {
@@ -769,11 +865,11 @@ __global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
                 // L2 round trips per task were ~2 % of the sweep with the convergence test on)
                 const unsigned long long* word = reinterpret_cast<const unsigned long long*>(&a.ctl->iters);
                 unsigned long long w = ld_acquire_gpu(word);
-                if (it >= 2) {
+                if (ps >= 2 && !pa.noclose) {
                     const unsigned long long t0 = global_timer_ns();
-                    while ((int)(unsigned)(w & 0xffffffffull) < a.it + it - 1) {
+                    while ((int)(unsigned)(w & 0xffffffffull) < it_first - K) {
                         if (a.check && (unsigned)(w >> 32)) break;                      // nothing closes after convergence
-                        if (*((volatile int*)a.err) || global_timer_ns() - t0 > NSB_SPIN_TIMEOUT_NS) { *((volatile int*)a.err) = 1; stop = 1; break; }
+                        if (*((volatile int*)a.err) || global_timer_ns() - t0 > spin_timeout_ns(a.err)) { *((volatile int*)a.err) = 1; stop = 1; break; }
                         __nanosleep(64);
                         w = ld_acquire_gpu(word);
                     }
@@ -784,81 +880,42 @@ __global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
         }
         if (stop) break;
 
-        // ---- wait for the 3 x 3 neighbourhood of the previous iteration
-        if (it > 0) {
+        // ---- wait for the 3 x 3 neighbourhood of the previous pass
+        if (ps > 0) {
             int ok = 1;
             if (lane < 9) {
                 const int cc = chunk + lane / 3 - 1, ss = strip + lane % 3 - 1;
                 if (cc >= 0 && cc < a.n_chunks && ss >= 0 && ss < a.n_strips)
-                    ok = spin_gpu_ge(pa.done + (size_t)cc * a.n_strips + ss, pa.flag_base + (unsigned long long)it, a.err) ? 1 : 0;
+                    ok = spin_gpu_ge(pa.done + (size_t)cc * a.n_strips + ss, pa.flag_base + (unsigned long long)ps, a.err) ? 1 : 0;
             }
             ok = __all_sync(FULLM, ok);
             if (!ok) break;
             asm volatile("fence.proxy.async;" ::: "memory");   // other warps' generic stores -> this warp's TMA reads
         }
 
-        const int bo = (pa.buf0 + it + 1) & 1;              // buffer this iteration writes
-        const double* pin = pa.own_p[bo ^ 1];
-        double* pout = pa.own_p[bo];
+        const int bi = (pa.buf0 + ps) % 3;                  // buffer this pass reads
+        const int bo = (bi + 1) % 3;                        // ... and writes
 
-        const int g0 = strip * NSB_STRIP_GROUPS;
-        const int g = g0 + lane;
-        const int i0 = g * NSB_GROUP - NSB_COL0;
         LaneGeom lg;
-        bool all_inner = (g < a.n_groups);
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            lg.inner[k] = (i0 + k >= 1) && (i0 + k <= a.ni);
-            all_inner = all_inner && lg.inner[k];
-        }
-        lg.owner = (g < a.n_groups) && lane >= 1 && lane <= NSB_STRIP_GROUPS;
-        lg.ghostW = (i0 + 3 == 0);
-        const int kg = a.ni + 1 - i0;
-        lg.kGhostE = (kg >= 0 && kg <= 3) ? kg : -1;
-        lg.warpW = __any_sync(FULLM, lg.ghostW);
-        lg.warpE = __any_sync(FULLM, lg.kGhostE >= 0);
-        const bool edge_strip = !__all_sync(FULLM, all_inner);
-
         TaskCtx t;
-        t.jc0 = 1 + chunk * a.chunk_rows;
-        t.jc1 = min(t.jc0 + a.chunk_rows - 1, a.nj);
-        t.jstart = t.jc0 - 3;
-        t.nj = a.nj;
-        t.wall_bottom = !(MULTI && (a.wall_bottom == 0)); t.wall_top = !(MULTI && (a.wall_top == 0));
-        t.rlo = t.wall_bottom ? 1 : -1;
-        t.rhi = t.wall_top ? a.nj : a.nj + 2;
-        t.push_down = (MULTI && (!t.wall_bottom && t.jc0 <= 3));
-        t.push_up = (MULTI && (!t.wall_top && t.jc1 >= a.nj - 2));
-        t.pitch = a.pitch;
-        t.lane = lane;
-        t.zero = a.zero;
-        const long long coff = (long long)g0 * NSB_GROUP;
-        const long long row_first = (long long)(t.jstart + NSB_ROW0) * a.pitch;
-        t.pin_next = pin + row_first + coff;
-        t.rhs_next = a.rhs + row_first + coff;
-        t.j_next = t.jstart;
-        t.j_limit = min(t.jc1 + 3, a.nj + 3);
-        t.pout_row = pout + row_first - SOR_LAG_BLACK * a.pitch + coff + (long long)lane * NSB_GROUP;
-        t.down_col = pa.down_p[bo] + coff + (long long)lane * NSB_GROUP;
-        t.up_col = pa.up_p[bo] + coff + (long long)lane * NSB_GROUP;
-        t.down_nj = a.down_nj;
-        const int groups_here = min(32, a.n_groups - g0);
-        t.copy_bytes = (uint32_t)groups_here * 32u;
+        bool edge_strip;
+        sor_task_geometry<MULTI, K>(t, lg, edge_strip, a, strip, chunk, lane);
+        sor_task_buffers<K>(t, pa.own_p[bi], pa.own_p[bo], a.rhs, pa.down_p[bo], pa.up_p[bo], strip, lane);
         t.lds_lane = reinterpret_cast<const double*>(ring) + lane * NSB_GROUP;
         t.smem_base = smem_u32(ring);
         t.bar_base = bar_base;
 
-        // ---- y-slab: rows of the previous iteration pushed by the neighbouring ranks (their boundary
-        //      tasks of iteration it-1, strips s-1 .. s+1); a.seq = halo epoch of "before iteration 0"
-        if ((MULTI && (a.world > 1)) && it > 0) {
-            const bool need_down = !t.wall_bottom && t.jc0 - 3 <= 0;
-            const bool need_up = !t.wall_top && t.jc1 + 3 >= a.nj + 1;
+        // ---- y-slab: rows of the previous pass pushed by the neighbouring ranks (their boundary
+        //      tasks of pass ps-1, strips s-1 .. s+1); a.seq = halo epoch of "before pass 0"
+        if ((MULTI && (a.world > 1)) && (ps > 0 || pa.wait_first)) {
+            const bool need_down = !t.wall_bottom && t.jc0 - SorK<K>::HALO <= 0;
+            const bool need_up = !t.wall_top && t.jc1 + SorK<K>::HALO >= a.nj + 1;
             int ok2 = 1;
             if (lane < 3) {
                 const int sidx = strip - 1 + lane;
                 if (sidx >= 0 && sidx < a.n_strips) {
-                    if (need_down) ok2 = spin_until_ge(a.flag_from_down + sidx, a.seq + (unsigned long long)it, a.err) ? 1 : 0;
-                    if (need_up && ok2) ok2 = spin_until_ge(a.flag_from_up + sidx, a.seq + (unsigned long long)it, a.err) ? 1 : 0;
+                    if (need_down) ok2 = spin_until_ge(a.flag_from_down + sidx, a.seq + (unsigned long long)ps, a.err) ? 1 : 0;
+                    if (need_up && ok2) ok2 = spin_until_ge(a.flag_from_up + sidx, a.seq + (unsigned long long)ps, a.err) ? 1 : 0;
                 }
             }
             ok2 = __all_sync(FULLM, ok2);
@@ -866,12 +923,16 @@ __global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
             asm volatile("fence.proxy.async;" ::: "memory");
         }
 
-        double acc = sor_task<RECIP>(t, a.k, lg, edge_strip, full_par, empty_par);
-        acc = warp_sum(acc);
-        double* part = pa.partials2 + (size_t)(it & 1) * a.n_tasks;
-        if (lane == 0) part[tslot] = acc;
+        double accs[K];
+        sor_task<RECIP, K>(t, a.k, lg, edge_strip, full_par, empty_par, accs);
+        double* part = pa.partials2 + (size_t)(ps & 1) * NSB_SOR_KMAX * a.n_tasks;
+#pragma unroll
+        for (int q = 0; q < K; q++) {
+            const double v = warp_sum(accs[q]);
+            if (lane == 0) part[(size_t)q * a.n_tasks + tslot] = v;
+        }
 
-        // ---- publish: rows and partial are out
+        // ---- publish: rows and partials are out
         __threadfence();
         __syncwarp();
         unsigned long long tk = 0;
@@ -879,66 +940,59 @@ __global__ void SOR_KERNEL_ATTR sor_persist_kernel(const SorPersistArgs pa) {
             __threadfence_system();
             __syncwarp();
             if (lane == 0) {
-                if (t.push_down) st_release_sys(a.down_flag + strip, a.seq + (unsigned long long)it + 1ull);
-                if (t.push_up) st_release_sys(a.up_flag + strip, a.seq + (unsigned long long)it + 1ull);
+                if (t.push_down) st_release_sys(a.down_flag + strip, a.seq + (unsigned long long)ps + 1ull);
+                if (t.push_up) st_release_sys(a.up_flag + strip, a.seq + (unsigned long long)ps + 1ull);
             }
         }
         if (lane == 0) {
-            st_release_gpu(pa.done + tslot, pa.flag_base + (unsigned long long)it + 1ull);
-            tk = atomicAdd(pa.claim + 1 + (it & 3), 1ull);
+            st_release_gpu(pa.done + tslot, pa.flag_base + (unsigned long long)ps + 1ull);
+            tk = atomicAdd(pa.claim + 1 + (ps & 3), 1ull);
         }
         tk = __shfl_sync(FULLM, tk, 0);
         if (tk == (unsigned long long)a.n_tasks - 1ull) {
-            // this warp closes iteration `it`: band sums in the fixed order of the per-iteration kernel
+            // this warp closes pass `ps`: band sums in the fixed order of the per-iteration kernel, per sub-iteration.
+            // The band values are double-buffered by pass parity: the closer of pass ps-1 may still be reading its own.
             __threadfence();
-            if (lane == 0) pa.claim[1 + (it & 3)] = 0ull;
-            // 16 bands at a time, so that 16 loads per lane are in flight: one band after the other
-            // (an L2 round trip each) took ~0.5 us per band, 40 us for the 86 bands of 2048^2 -- as long as
-            // the iteration itself, and iteration n+2 waits for this closing (ncu source page, 2048^2:
-            // half of all warp samples sat in the `iters` poll above).  Per band the additions are those
-            // of warp_ordered_sum (lane-strided partials in q order, then the butterfly): same bits.
-            for (int b0 = 0; b0 < a.n_chunks; b0 += 16) {
-                double sb[16];
+            if (lane == 0) pa.claim[1 + (ps & 3)] = 0ull;
+            double* bands = pa.bandvals2 + (size_t)(ps & 1) * NSB_SOR_KMAX * (a.n_chunks + 1);
+            if (!pa.noclose) {
 #pragma unroll
-                for (int u = 0; u < 16; u++) sb[u] = 0.0;
-                for (int q = lane; q < a.n_strips; q += 32) {
-#pragma unroll
-                    for (int u = 0; u < 16; u++)
-                        if (b0 + u < a.n_chunks) sb[u] += __ldcg(part + (size_t)(b0 + u) * a.n_strips + q);
-                }
-#pragma unroll
-                for (int u = 0; u < 16; u++) sb[u] = warp_sum(sb[u]);
-                if (lane == 0) {
-#pragma unroll
-                    for (int u = 0; u < 16; u++)
-                        if (b0 + u < a.n_chunks) a.bandvals[b0 + u] = sb[u];
-                }
+                for (int q = 0; q < K; q++)
+                    sor_band_sums(part + (size_t)q * a.n_tasks, bands + (size_t)q * (a.n_chunks + 1), a.n_chunks, a.n_strips, lane);
             }
             __threadfence();
             __syncwarp();
             // iterations close in order; nothing closes (and no reduction round is spent) after the one
             // that converged -- every rank sees the same residual bits, so every rank decides the same
-            int skip = 0;
-            if (lane == 0) {
+            int skip = pa.noclose;
+            if (lane == 0 && !skip) {
                 const unsigned long long t0 = global_timer_ns();
-                while (ld_acquire_gpu_s32(&a.ctl->iters) < a.it + it) {
+                while (ld_acquire_gpu_s32(&a.ctl->iters) < it_first) {
                     if (a.check && ld_acquire_gpu_s32(&a.ctl->converged)) break;
-                    if (global_timer_ns() - t0 > NSB_SPIN_TIMEOUT_NS) { *((volatile int*)a.err) = 1; skip = 1; break; }
+                    if (global_timer_ns() - t0 > spin_timeout_ns(a.err)) { *((volatile int*)a.err) = 1; skip = 1; break; }
                     __nanosleep(64);
                 }
                 if (a.check && ld_acquire_gpu_s32(&a.ctl->converged)) skip = 1;
             }
             skip = __shfl_sync(FULLM, skip, 0);
-            if (!skip) {
+#pragma unroll
+            for (int q = 0; q < K; q++) {
+                if (skip) break;
+                const double* bq = bands + (size_t)q * (a.n_chunks + 1);
                 double tot;
                 if ((MULTI && (a.world > 1))) {
-                    const unsigned long long round = pa.round0 + (unsigned long long)it;
-                    slab_red_contribute_warp(a.red, round, 1, a.bandvals, lane);
+                    const unsigned long long round = pa.round0 + (unsigned long long)(ps * K + q);
+                    slab_red_contribute_warp(a.red, round, 1, bq, lane);
                     slab_red_finish_sum_warp(a.red, round, lane, &tot);
                 } else {
-                    tot = warp_ordered_sum(a.bandvals, a.n_chunks, lane);
+                    tot = warp_ordered_sum(bq, a.n_chunks, lane);
                 }
-                if (lane == 0) sor_close_iteration(tot, a.ctl, a.it + it, a.k.cells);
+                int conv = 0;
+                if (lane == 0) {
+                    sor_close_iteration(tot, a.ctl, it_first + q, a.k.cells);
+                    conv = (a.check && a.ctl->converged) ? 1 : 0;
+                }
+                skip = __shfl_sync(FULLM, conv, 0);          // the later sub-iterations of a converged pass are not closed
             }
             __syncwarp();
         }
@@ -951,9 +1005,12 @@ static SorStreamFn sor_stream_fn(bool recip, bool multi) {
     return recip ? (multi ? sor_stream_kernel<true, true> : sor_stream_kernel<true, false>)
                  : (multi ? sor_stream_kernel<false, true> : sor_stream_kernel<false, false>);
 }
-static SorPersistFn sor_persist_fn(bool recip, bool multi) {
-    return recip ? (multi ? sor_persist_kernel<true, true> : sor_persist_kernel<true, false>)
-                 : (multi ? sor_persist_kernel<false, true> : sor_persist_kernel<false, false>);
+static SorPersistFn sor_persist_fn(bool recip, bool multi, int k) {
+    if (k == 2)
+        return recip ? (multi ? sor_persist_kernel<true, true, 2> : sor_persist_kernel<true, false, 2>)
+                     : (multi ? sor_persist_kernel<false, true, 2> : sor_persist_kernel<false, false, 2>);
+    return recip ? (multi ? sor_persist_kernel<true, true, 1> : sor_persist_kernel<true, false, 1>)
+                 : (multi ? sor_persist_kernel<false, true, 1> : sor_persist_kernel<false, false, 1>);
 }
 
 // y-slabs: only when every rank sits on a GPU of its own -- the kernels of neighbouring ranks wait
@@ -962,6 +1019,24 @@ static SorPersistFn sor_persist_fn(bool recip, bool multi) {
 int nsb_sor_persist_supported(const nsb_ctx* c) {
     if (c->chunk_rows < 4) return 0;
     return c->world == 1 || (c->connected && c->peers_distinct);
+}
+
+// Sub-iterations per pass of the persistent sweep for this context.  Default 1: on a B200 the two-iteration pass
+// halves the DRAM traffic (0.855 GB instead of 1.676 GB per iteration at 8192^2, ncu) but is not faster -- the sweep
+// is bound by instruction latency, not by HBM, once the reads are halved (255.6 us against 250.7 us per iteration,
+// profiles/r2c_*) -- so it is there on request: NSB_SOR_K=2 or nsb_options.sor_pass_k = 2.
+// Falls back to 1 where the chunks or the slab are too short for the 5-row halo.
+static int sor_k_wanted(const nsb_ctx* c) {
+    int k = c->O.sor_pass_k >= 1 && c->O.sor_pass_k <= NSB_SOR_KMAX ? c->O.sor_pass_k : 1;
+    const char* env = getenv("NSB_SOR_K");
+    if (env && atoi(env) >= 1 && atoi(env) <= NSB_SOR_KMAX) k = atoi(env);
+    return k;
+}
+int nsb_sor_pass_k(const nsb_ctx* c) {
+    int k = sor_k_wanted(c);
+    if (c->chunk_rows < 2 * SorK<2>::HALO) k = 1;
+    if (c->world > 1 && c->g.nj < 2 * SorK<2>::HALO) k = 1;
+    return k;
 }
 
 // world > 1: the closing of an iteration is its own one-block kernel, so that the sweep kernel never
@@ -984,18 +1059,19 @@ cudaError_t nsb_launch_sor_close(nsb_ctx* c, int it, int check) {
 // Planning: strips are fixed (120 columns); pick an even chunk height that fills whole waves.
 
 // Chunk height of the persistent sweep (pure host arithmetic, also exported for the CPU tests):
-// `slots` = resident warps of the sweep kernel on the device, recip = reciprocal-product arithmetic.
-extern "C" int nsb_plan_chunk_rows(int ni, int nj, long long slots, int recip) {
+// `slots` = resident warps of the sweep kernel on the device, recip = reciprocal-product arithmetic,
+// k = sub-iterations per pass.
+extern "C" int nsb_plan_chunk_rows_k(int ni, int nj, long long slots, int recip, int k) {
     const long long n_strips = (ni + NSB_STRIP_COLS - 1) / NSB_STRIP_COLS;
     if (slots < 1) slots = 1;
     int best = 16;
     double best_cost = 1e300;
     // Chunk height of the persistent sweep, 16 .. 128 rows: minimise
-    //     max(tasks per resident warp and iteration, floor) x (rows + 18),   floor = 1.6
+    //     max(tasks per resident warp and pass, floor) x (rows + 18),   floor = 1.6
     // -- a task costs its rows plus ~18 row-steps of overhead (3 + 3 halo rows, 8 steps of pipeline
-    // fill, claim / flag waits), and below ~1.6 tasks per warp there is nothing to overlap the
-    // dependency waits between two iterations with (4096^2: 50 chunks of 82 rows = one task per warp
-    // 110 us per iteration, 86 chunks of 48 rows 90 us).  Above 128 rows the tail of a launch and the
+    // fill, claim / flag waits; 5 + 5 halo rows and 3 more steps of drain with k = 2), and below ~1.6 tasks per warp
+    // there is nothing to overlap the dependency waits between two passes with (4096^2: 50 chunks of 82 rows = one task
+    // per warp 110 us per iteration, 86 chunks of 48 rows 90 us).  Above 128 rows the tail of a launch and the
     // balance between SMs suffer (8192^2: 240 rows 298 us, 128 rows 265 us).  Measured optima
     // (profiles/r1h_chunk_sweep2.txt): 2048^2 16-24, 3072^2 32, 4096^2 48, 5120^2 48-80, 6144^2 64-112,
     // 7168^2 96-104, 8192^2 120-128; the model picks 16, 28, 50, 78, 112, 128, 128.
@@ -1003,34 +1079,38 @@ extern "C" int nsb_plan_chunk_rows(int ni, int nj, long long slots, int recip) {
     // warps counts for more: the measured optima sit at ~2.7 tasks per warp (4096^2 32-48 rows, 5120^2 48,
     // 6144^2 64-80, 7168^2 90, 8191^2 112; profiles/r1h_chunk_sweep2.txt), hence the higher floor.
     const double floor_tasks = recip ? 1.6 : 2.6;
+    const int overhead = k >= 2 ? 25 : 18;
     for (int rows = 16; rows <= 128; rows += 2) {
         const long long chunks = (nj + rows - 1) / rows;
         const double per_warp = (double)(chunks * n_strips) / (double)slots;
-        const double cost = (per_warp > floor_tasks ? per_warp : floor_tasks) * (rows + 18);
+        const double cost = (per_warp > floor_tasks ? per_warp : floor_tasks) * (rows + overhead);
         if (cost < best_cost - 1e-9) { best_cost = cost; best = rows; }
         if (rows >= nj) break;
     }
     return best;
 }
+extern "C" int nsb_plan_chunk_rows(int ni, int nj, long long slots, int recip) { return nsb_plan_chunk_rows_k(ni, nj, slots, recip, 1); }
 
 void nsb_sor_plan(nsb_ctx* c) {
     const int ni = c->g.ni, nj = c->g.nj;
     // function attributes are per device: set them for the device of every context that is planned
     for (int v = 0; v < 4; v++) {
-        cudaFuncSetAttribute((const void*)sor_stream_fn(v & 1, v & 2), cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES);
-        cudaFuncSetAttribute((const void*)sor_persist_fn(v & 1, v & 2), cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES);
+        cudaFuncSetAttribute((const void*)sor_stream_fn(v & 1, v & 2), cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES(1));
+        cudaFuncSetAttribute((const void*)sor_persist_fn(v & 1, v & 2, 1), cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES(1));
+        cudaFuncSetAttribute((const void*)sor_persist_fn(v & 1, v & 2, 2), cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES(2));
     }
     c->n_strips = (ni + NSB_STRIP_COLS - 1) / NSB_STRIP_COLS;
+    const int k = sor_k_wanted(c);
     int blocks_per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, (const void*)sor_stream_fn(c->use_recip, c->world > 1), SOR_THREADS,
-                                                  SOR_SMEM_BYTES);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, (const void*)sor_persist_fn(c->use_recip, c->world > 1, k), SOR_THREADS,
+                                                  SOR_SMEM_BYTES(k));
     if (blocks_per_sm < 1) blocks_per_sm = 1;
     const long long slots = (long long)c->sm_count * blocks_per_sm * SOR_WARPS;
     int best = 0;
     if (c->O.sor_chunk_rows > 0) {
         best = (c->O.sor_chunk_rows + 1) & ~1;
     } else {
-        best = nsb_plan_chunk_rows(ni, nj, slots, c->use_recip ? 1 : 0);
+        best = nsb_plan_chunk_rows_k(ni, nj, slots, c->use_recip ? 1 : 0, k);
     }
     if (best < 2) best = 2;
     c->chunk_rows = best;
@@ -1081,30 +1161,35 @@ cudaError_t nsb_launch_sor_stream_iter(nsb_ctx* c, int it, const double* pin, do
         }
     }
     const int blocks = (a.n_tasks + SOR_WARPS - 1) / SOR_WARPS;
-    sor_stream_fn(c->use_recip, c->world > 1)<<<blocks, SOR_THREADS, SOR_SMEM_BYTES, c->stream>>>(a);
+    sor_stream_fn(c->use_recip, c->world > 1)<<<blocks, SOR_THREADS, SOR_SMEM_BYTES(1), c->stream>>>(a);
     return NSB_LAUNCHED(c, 1);
 }
 
-// All `n_iter` iterations of a solve in one launch (single slab).  Iteration 0 reads pbuf[pcur].
-cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int n_iter, int check) {
-    if (n_iter <= 0) return cudaSuccess;
+// One launch of the persistent sweep: `n_pass` passes of `k` iterations each.  Pass 0 reads pbuf[buf_in] (0..2) and the
+// buffers rotate; `it0` = number of the first iteration inside the current solve.  noclose: replay of an iteration that
+// is already closed.  wait_first (y-slabs): the halo rows of pbuf[buf_in] are still being pushed by the neighbours'
+// previous launch of this solve.
+cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int k, int n_pass, int it0, int check, int buf_in, int noclose, int wait_first) {
+    if (n_pass <= 0) return cudaSuccess;
     SorPersistArgs pa;
     memset(&pa, 0, sizeof pa);
     SorStreamArgs& a = pa.s;
-    a.pin = c->pbuf[c->pcur]; a.pout = c->pbuf[c->pcur ^ 1]; a.rhs = c->rhs;
+    a.pin = c->pbuf[buf_in]; a.pout = c->pbuf[(buf_in + 1) % 3]; a.rhs = c->rhs;
     a.pitch = c->g.pitch; a.ni = c->g.ni; a.nj = c->g.nj;
     a.chunk_rows = c->chunk_rows; a.n_strips = c->n_strips; a.n_tasks = c->n_partials; a.n_chunks = c->n_chunks;
     a.n_groups = (int)(c->g.pitch / NSB_GROUP);
-    a.it = 0; a.check = check; a.zero = 0u;
+    a.it = it0; a.check = check; a.zero = 0u;
+    a.dbg_fixed_loads = getenv("NSB_DEBUG_FIXED_LOADS") ? 1 : 0;
     a.k = nsb_make_sor_coef(c, (long long)c->g.ni * (long long)c->J);     // main.cu:588: the GLOBAL cell count
     a.partials = c->d_partials; a.bandvals = c->d_bandvals; a.ctl = c->d_ctl;
     a.world = c->world; a.wall_bottom = c->wall_bottom; a.wall_top = c->wall_top;
     a.err = &c->d_sync->error;
-    a.seq = c->seq;
+    a.seq = wait_first ? c->seq_tail : c->seq;
     a.red = nsb_slab_red(c);
-    pa.round0 = c->red_round;
-    pa.buf0 = c->pcur;
-    for (int k = 0; k < 2; k++) { pa.own_p[k] = c->pbuf[k]; pa.down_p[k] = c->pbuf[k]; pa.up_p[k] = c->pbuf[k]; }
+    pa.round0 = c->red_round + (unsigned long long)it0;
+    pa.buf0 = buf_in;
+    pa.noclose = noclose; pa.wait_first = wait_first;
+    for (int q = 0; q < 3; q++) { pa.own_p[q] = c->pbuf[q]; pa.down_p[q] = c->pbuf[q]; pa.up_p[q] = c->pbuf[q]; }
     a.down_nj = 0;
     a.flag_from_down = c->d_sorflag; a.flag_from_up = c->d_sorflag + c->n_strips;
     a.down_flag = c->d_sorflag; a.up_flag = c->d_sorflag;
@@ -1112,32 +1197,36 @@ cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int n_iter, int check) {
         if (!c->connected) return cudaErrorNotReady;
         if (!c->wall_bottom) {
             const SlabPeer& d = c->peer[c->rank - 1];
-            pa.down_p[0] = d.p[0]; pa.down_p[1] = d.p[1]; a.down_nj = d.nj;
+            for (int q = 0; q < 3; q++) pa.down_p[q] = d.p[q];
+            a.down_nj = d.nj;
             a.down_flag = d.sorflag + c->n_strips;             // I am its UPPER neighbour
         }
         if (!c->wall_top) {
             const SlabPeer& u = c->peer[c->rank + 1];
-            pa.up_p[0] = u.p[0]; pa.up_p[1] = u.p[1];
+            for (int q = 0; q < 3; q++) pa.up_p[q] = u.p[q];
             a.up_flag = u.sorflag;                             // I am its LOWER neighbour
         }
     }
-    c->seq += (unsigned long long)n_iter + 1ull;               // halo epochs: iterations ATTEMPTED, like flag_base
-    pa.n_iter = n_iter;
-    pa.claim = c->d_claim; pa.done = c->d_done; pa.partials2 = c->d_partials2;
+    // halo epochs: pass q of this launch publishes a.seq + q + 1.  A launch that continues the previous one
+    // (wait_first) starts at the epoch its last pass published; any other launch starts above everything published.
+    c->seq_tail = a.seq + (unsigned long long)n_pass;
+    c->seq = c->seq_tail + 1ull;
+    pa.n_pass = n_pass;
+    pa.claim = c->d_claim; pa.done = c->d_done; pa.partials2 = c->d_partials2; pa.bandvals2 = c->d_bandvals2;
     pa.flag_base = c->flag_base;
-    c->flag_base += (unsigned long long)n_iter + 1ull;
+    c->flag_base += (unsigned long long)n_pass + 1ull;
     int bps = 0;
-    const SorPersistFn kern = sor_persist_fn(c->use_recip, c->world > 1);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (const void*)kern, SOR_THREADS, SOR_SMEM_BYTES);
+    const SorPersistFn kern = sor_persist_fn(c->use_recip, c->world > 1, k);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (const void*)kern, SOR_THREADS, SOR_SMEM_BYTES(k));
     if (bps < 1) bps = 1;
-    const long long want = ((long long)n_iter * a.n_tasks + SOR_WARPS - 1) / SOR_WARPS;
+    const long long want = ((long long)n_pass * a.n_tasks + SOR_WARPS - 1) / SOR_WARPS;
     long long blocks = (long long)c->sm_count * bps;
     if (blocks > want) blocks = want;
-    // at most two iterations are in flight at any time: more warps than that would only poll flags
+    // at most two passes are in flight at any time: more warps than that would only poll flags
     const long long useful = (2LL * a.n_tasks + SOR_WARPS - 1) / SOR_WARPS + 1;
     if (blocks > useful) blocks = useful;
     cudaError_t e = cudaMemsetAsync(c->d_claim, 0, 8 * sizeof(unsigned long long), c->stream);
     if (e != cudaSuccess) return e;
-    kern<<<(int)blocks, SOR_THREADS, SOR_SMEM_BYTES, c->stream>>>(pa);
+    kern<<<(int)blocks, SOR_THREADS, SOR_SMEM_BYTES(k), c->stream>>>(pa);
     return NSB_LAUNCHED(c, 1);
 }

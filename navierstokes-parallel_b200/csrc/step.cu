@@ -192,11 +192,19 @@ static int sor_iterate(nsb_ctx** cs, int n, int max_it, int check) {
         CU(c0, nsb_launch_sor_lex(c0, max_it, check));
         return NSB_OK;
     }
-    if (engine == NSB_SOR_STREAM) {                            // every iteration of the solve in one launch per rank
+    if (engine == NSB_SOR_STREAM) {
+        // Every iteration of the solve in one launch per rank: max_it / 2 passes of TWO iterations each (temporal
+        // blocking), then one single-iteration pass when max_it is odd.  Both launches are enqueued at once: the
+        // second looks at the device-side `converged` flag and returns without work if the first one met the threshold.
         for (int r = 0; r < n; r++) {
             nsb_ctx* c = cs[r];
             CU(c, cudaSetDevice(c->device));
-            CU(c, nsb_launch_sor_persist(c, max_it, check));
+            const int k = nsb_sor_pass_k(c);
+            const int passes = k > 1 ? max_it / k : 0;
+            const int tail = max_it - passes * k;
+            c->st_k = k; c->st_passes = passes; c->st_tail = tail; c->st_buf0 = c->pcur;
+            if (passes > 0) CU(c, nsb_launch_sor_persist(c, k, passes, 0, check, c->pcur, 0, 0));
+            if (tail > 0) CU(c, nsb_launch_sor_persist(c, 1, tail, passes * k, check, (c->pcur + passes) % 3, 0, passes > 0 ? 1 : 0));
         }
         return NSB_OK;
     }
@@ -242,12 +250,41 @@ int nsb_ph_sor_end(nsb_ctx* c, int unused) {
         if (werr) return nsb_fail(c, NSB_ERR_CUDA, "SOR: a wait inside the sweep kernel timed out (rank %d)", c->rank);
     }
     const int iters = c->h_ctl[1].iters;
-    if (c->last_sor_engine == NSB_SOR_STREAM || c->last_sor_engine == NSB_SOR_STREAM_LAUNCH) {
+    if (c->last_sor_engine == NSB_SOR_STREAM) {
+        // Which of the three rotating buffers holds iterate `iters`?  Pass q of the K-iteration launch read buffer
+        // buf0 + q and wrote buf0 + q + 1 (mod 3).  If the solve stopped inside a pass (its first sub-iteration met the
+        // threshold), that iterate was never stored: the pass's input is still intact (the buffer is rewritten two passes
+        // later, and nothing runs that far after convergence), so ONE single-iteration pass from it reproduces the
+        // iterate bit for bit (same task shape, same arithmetic); it does not close anything again.
+        const int k = c->st_k, in_passes = c->st_passes * k;
+        int buf;
+        if (iters <= in_passes) {
+            const int full = iters / k, rest = iters - full * k;
+            buf = (c->st_buf0 + full) % 3;
+            if (rest > 0) {
+                CU(c, nsb_launch_sor_persist(c, 1, rest, iters - rest, 0, buf, 1, 0));
+                CU(c, cudaStreamSynchronize(c->stream));
+                buf = (buf + rest) % 3;
+            }
+        } else {
+            buf = (c->st_buf0 + c->st_passes + (iters - in_passes)) % 3;
+        }
+        // between solves the pressure lives in pbuf[0] or pbuf[1] (the other engines flip between those two):
+        // rename the buffers instead of copying.  Every rank of a decomposition sees the same iteration counts,
+        // so all ranks rename alike and the peers' tables follow.
+        if (buf == 2) {
+            const int other = c->pcur ^ 1;
+            double* tmp = c->pbuf[2]; c->pbuf[2] = c->pbuf[other]; c->pbuf[other] = tmp;
+            for (int r = 0; r < c->world; r++) { double* q = c->peer[r].p[2]; c->peer[r].p[2] = c->peer[r].p[other]; c->peer[r].p[other] = q; }
+            buf = other;
+        }
+        c->pcur = buf;
+    } else if (c->last_sor_engine == NSB_SOR_STREAM_LAUNCH) {
         c->pcur = (c->pcur + iters) & 1;
         // per-launch sweeps: the other buffer still holds the previous iterate, which the ghost
         // fix-up reads.  The persistent sweep stores the ghost cells itself (iterations that ran past
         // the converged one may have overwritten the other buffer).
-        if (iters > 0 && c->last_sor_engine == NSB_SOR_STREAM_LAUNCH)
+        if (iters > 0)
             CU(c, nsb_launch_sor_finish_ghosts(c, c->pbuf[c->pcur], c->pbuf[c->pcur ^ 1]));
     }
     if (c->last_sor_engine != NSB_SOR_STREAM) c->seq += (unsigned long long)iters;   // (the persistent launch advanced it)
@@ -483,8 +520,8 @@ static int group_xfer(nsb_group* g, int field, double* host, int layout, bool up
     int rc = NSB_OK;
     for (int k = 0; k < g->n && rc == NSB_OK; k++) {
         nsb_ctx* c = g->c[k];
-        int lo = up ? -2 : (c->wall_bottom ? 0 : 1);                 // local rows to move
-        int hi = up ? c->g.nj + 3 : (c->wall_top ? c->g.nj + 1 : c->g.nj);
+        int lo = up ? 1 - NSB_HALO_ROWS : (c->wall_bottom ? 0 : 1);   // local rows to move
+        int hi = up ? c->g.nj + NSB_HALO_ROWS : (c->wall_top ? c->g.nj + 1 : c->g.nj);
         if (c->j_lo + lo < 0) lo = -c->j_lo;
         if (c->j_lo + hi > c->J + 1) hi = c->J + 1 - c->j_lo;
         rc = nsb_xfer_rows(c, field, x + (size_t)(c->j_lo + lo) * nx, lo, hi - lo + 1, up ? 1 : 0);

@@ -417,6 +417,9 @@ def test_host_grid_api_SOR_and_FG():
     ob.lib().orc_FG(ob._ptr(F2), ob._ptr(G2), ob._ptr(uf), ob._ptr(vf), ni, nj, 100.0, 0.0, 0.0, 0.01, dx, dy, 0.3)
     assert np.array_equal(F, F2) and np.array_equal(G, G2)
     assert L.nsb_max_mat(ni, nj, m.rows(u)) == ob.lib().orc_max_mat(ni, nj, ob._ptr(uf))
+    # ... and on the v shape (rows of j_max+1 doubles: nothing past a row's end may be read -- the last row of v ends
+    # the allocation here, so an over-read would run off the numpy buffer)
+    assert L.nsb_max_mat(ni, nj, m.rows(v)) == ob.lib().orc_max_mat(ni, nj, ob._ptr(vf))
     L.nsb_host_api_reset()
 
 
