@@ -12,7 +12,9 @@
  *   - stderr: accumulated SOR seconds "%.6f", no newline, last thing written (main.c:153);
  *   - unknown problem type: message + EXIT_FAILURE (main.c:105-108);
  *   - field dumps every n_print-th step to out/<n> are DISABLED in both reference mains
- *     (main.c:138-143 is commented out); set NSB_OUTPUT=1 to enable them here;
+ *     (main.c:138-143 is commented out); set NSB_OUTPUT=1 to enable them here (single GPU and NSB_GPUS alike).
+ *     The dump is overlapped with the following time steps (nsb_output_async: device snapshot, side-stream copy,
+ *     host formatting threads); NSB_OUTPUT=sync writes it before the loop goes on, like the reference would;
  *   - NSB_GPUS=n (n > 1) cuts the domain into n y-slabs, one per GPU of the box (new: the reference
  *     is single-GPU).
  *
@@ -68,11 +70,14 @@ int main(int argc, char* argv[])
         if (verbose)
             fprintf(stderr, "step %d t %.10g dt %.10g umax %.6g vmax %.6g gamma %.6g normp %.6g its %d res %.6g\n",
                     n, info.t, info.dt, info.u_max, info.v_max, info.gamma, info.norm_p, info.sor_iters, info.res);
-        if (!grp && dump && dump[0] == '1' && P.n_print > 0 && n % P.n_print == 0) { /* main.c:138-143 */
+        if (dump && (dump[0] == '1' || dump[0] == 's') && P.n_print > 0 && n % P.n_print == 0) { /* main.c:138-143 */
             char prefix[64];
+            const int sync = dump[0] == 's';
             snprintf(prefix, sizeof prefix, "out/%d", n_out);
-            if (nsb_output(ctx, t, prefix) != NSB_OK) {
-                perror(nsb_last_error(ctx));
+            if (grp) rc = sync ? nsb_group_output(grp, t, prefix) : nsb_group_output_async(grp, t, prefix);
+            else rc = sync ? nsb_output(ctx, t, prefix) : nsb_output_async(ctx, t, prefix);
+            if (rc != NSB_OK) {
+                perror(grp ? nsb_group_last_error(grp) : nsb_last_error(ctx));       /* io.c:83-87 */
                 exit(EXIT_FAILURE);
             }
             printf("Output created!\n");                                             /* io.c:118 */
@@ -87,6 +92,10 @@ int main(int argc, char* argv[])
         else nsb_get_center(ctx, &uc, &vc);
         printf("U-CENTER: %.6f\n", uc);                                              /* main.c:148 */
         printf("V-CENTER: %.6f\n", vc);                                              /* main.c:149 */
+    }
+    if ((grp ? nsb_group_output_wait(grp) : nsb_output_wait(ctx)) != NSB_OK) {       /* the last dump, if still being written */
+        perror(grp ? nsb_group_last_error(grp) : nsb_last_error(ctx));
+        exit(EXIT_FAILURE);
     }
     fflush(stdout);
     fprintf(stderr, "%.6f", grp ? nsb_group_sor_seconds(grp) : nsb_sor_seconds(ctx)); /* main.c:153 */

@@ -160,8 +160,14 @@ long long nsb_launch_count(const nsb_ctx* ctx);
 /* host <-> HBM.  host holds (i_max+2)*(j_max+2) doubles in the given layout. */
 int nsb_upload(nsb_ctx* ctx, int field, const double* host, int layout);
 int nsb_download(nsb_ctx* ctx, int field, double* host, int layout);
-/* io.h:31 output(): writes <prefix>_u.txt, _v.txt, _p.txt in the reference's text format */
+/* io.h:31 output(): writes <prefix>_u.txt, _v.txt, _p.txt in the reference's text format (io.c:61-120), byte for
+ * byte.  nsb_output returns when the files are closed.  nsb_output_async snapshots the fields on the device and
+ * returns at once: the copy to the host runs on a side stream and the text is produced by host threads while the
+ * time loop goes on (the n_print cadence of main.c:138-143 without stalling the solver); nsb_output_wait (also
+ * implied by the next dump and by nsb_destroy) returns the status of the dump in flight. */
 int nsb_output(nsb_ctx* ctx, double t, const char* prefix);
+int nsb_output_async(nsb_ctx* ctx, double t, const char* prefix);
+int nsb_output_wait(nsb_ctx* ctx);
 
 /* device pointers for zero-copy interop (e.g. torch): base of the padded grid, its pitch in
  * doubles, the column offset of i = 0 and the row offset of j = 0 */
@@ -202,6 +208,10 @@ double nsb_group_sor_seconds(const nsb_group* g);
 int nsb_group_upload(nsb_group* g, int field, const double* host, int layout);     /* whole domain */
 int nsb_group_download(nsb_group* g, int field, double* host, int layout);
 int nsb_group_get_center(nsb_group* g, double* u_c, double* v_c);
+/* output() for the whole domain: every slab contributes its rows to the same three files */
+int nsb_group_output(nsb_group* g, double t, const char* prefix);
+int nsb_group_output_async(nsb_group* g, double t, const char* prefix);
+int nsb_group_output_wait(nsb_group* g);
 
 /* ---------------------------------------------------------------- B. host-grid API
  * Same argument lists as the reference functions.  Grids are the reference's jagged `double**`

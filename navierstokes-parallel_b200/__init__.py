@@ -109,6 +109,8 @@ ABI = {
     "nsb_upload": (C.c_int, [C.c_void_p, C.c_int, dbl_p, C.c_int]),
     "nsb_download": (C.c_int, [C.c_void_p, C.c_int, dbl_p, C.c_int]),
     "nsb_output": (C.c_int, [C.c_void_p, C.c_double, C.c_char_p]),
+    "nsb_output_async": (C.c_int, [C.c_void_p, C.c_double, C.c_char_p]),
+    "nsb_output_wait": (C.c_int, [C.c_void_p]),
     "nsb_device_view": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_longlong), int_p, int_p]),
     "nsb_SOR": (C.c_int, [dbl_pp, C.c_int, C.c_int, C.c_double, C.c_double, dbl_pp, dbl_pp, C.c_double, C.c_double, C.c_int]),
     "nsb_SOR_iters": (C.c_int, [dbl_pp, C.c_int, C.c_int, C.c_double, C.c_double, dbl_pp, dbl_pp, C.c_double, C.c_double, C.c_int, int_p, dbl_p]),
@@ -137,6 +139,9 @@ ABI = {
     "nsb_group_upload": (C.c_int, [C.c_void_p, C.c_int, dbl_p, C.c_int]),
     "nsb_group_download": (C.c_int, [C.c_void_p, C.c_int, dbl_p, C.c_int]),
     "nsb_group_get_center": (C.c_int, [C.c_void_p, dbl_p, dbl_p]),
+    "nsb_group_output": (C.c_int, [C.c_void_p, C.c_double, C.c_char_p]),
+    "nsb_group_output_async": (C.c_int, [C.c_void_p, C.c_double, C.c_char_p]),
+    "nsb_group_output_wait": (C.c_int, [C.c_void_p]),
 }
 
 
@@ -298,8 +303,13 @@ class Solver:
     def launch_count(self):
         return self._L.nsb_launch_count(self._h)
 
-    def output(self, t, prefix):
-        self._ck(self._L.nsb_output(self._h, t, os.fsencode(prefix)))
+    def output(self, t, prefix, wait=True):
+        """io.h:31 output(); wait=False: returns once the fields are snapshotted, output_wait() joins the writer."""
+        f = self._L.nsb_output if wait else self._L.nsb_output_async
+        self._ck(f(self._h, t, os.fsencode(prefix)))
+
+    def output_wait(self):
+        self._ck(self._L.nsb_output_wait(self._h))
 
     # -- transfers
     def upload(self, field, a: np.ndarray, layout=LAYOUT_REF):
@@ -415,6 +425,13 @@ class Group:
         a, b = C.c_double(), C.c_double()
         self._ck(self._L.nsb_group_get_center(self._h, C.byref(a), C.byref(b)))
         return a.value, b.value
+
+    def output(self, t, prefix, wait=True):
+        f = self._L.nsb_group_output if wait else self._L.nsb_group_output_async
+        self._ck(f(self._h, t, os.fsencode(prefix)))
+
+    def output_wait(self):
+        self._ck(self._L.nsb_group_output_wait(self._h))
 
     def upload(self, field, a: np.ndarray, layout=LAYOUT_REF):
         a = np.ascontiguousarray(a, dtype=np.float64)

@@ -81,6 +81,7 @@ extern "C" void nsb_destroy(nsb_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    nsb_out_release(c);                                        // joins a dump still being written (output.cu)
     for (int r = 0; r < c->world && r < NSB_MAX_RANKS; r++)
         if (r != c->rank && c->peer[r].mapped_ipc && c->peer[r].base) cudaIpcCloseMemHandle(c->peer[r].base);
     if (c->arena) cudaFree(c->arena);
@@ -415,45 +416,6 @@ extern "C" int nsb_download(nsb_ctx* c, int field, double* host, int layout) {
     }
     CU(c, cudaStreamSynchronize(c->stream));
     return NSB_OK;
-}
-
-// ------------------------------------------------------------------ output(), io.c:61-120
-// Row order of the files is j-major with i running inside a row: exactly the x-fastest layout, so
-// the three grids are downloaded as they lie and formatted row by row.
-extern "C" int nsb_output(nsb_ctx* c, double t, const char* prefix) {
-    if (!c || !prefix) return NSB_ERR_ARG;
-    const size_t nx = (size_t)c->g.ni + 2, ny = (size_t)c->g.nj + 2;
-    double* host = (double*)malloc(nx * ny * sizeof(double));
-    if (!host) return fail(c, NSB_ERR_ARG, "out of host memory");
-    const char* suffix[3] = {"_u.txt", "_v.txt", "_p.txt"};
-    const int fields[3] = {NSB_U, NSB_V, NSB_P};
-    FILE* fp[3] = {NULL, NULL, NULL};
-    char name[1024];
-    for (int k = 0; k < 3; k++) {
-        snprintf(name, sizeof name, "%s%s", prefix, suffix[k]);
-        fp[k] = fopen(name, "w");
-    }
-    if (!fp[0] || !fp[1] || !fp[2]) {
-        for (int k = 0; k < 3; k++) if (fp[k]) fclose(fp[k]);
-        free(host);
-        return fail(c, NSB_ERR_IO, "Error opening one ore more output files. Make sure the directory 'out' exists.");
-    }
-    int rc = NSB_OK;
-    for (int k = 0; k < 3 && rc == NSB_OK; k++) {
-        rc = nsb_download(c, fields[k], host, NSB_LAYOUT_XFAST);
-        if (rc) break;
-        fprintf(fp[k], "%.5f\n%.5f\n%.5f\n", t, c->P.a, c->P.b);          // io.c:89-99
-        const size_t ncol = (k == 0) ? nx - 1 : nx;                     // u omits i = i_max+1
-        const size_t nrow = (k == 1) ? ny - 1 : ny;                     // v omits j = j_max+1 ...
-        for (size_t j = 0; j < ny; j++) {
-            if (j < nrow)
-                for (size_t i = 0; i < ncol; i++) fprintf(fp[k], "%.5f ", host[j * nx + i]);
-            fputc('\n', fp[k]);                                         // ... but keeps its newline
-        }
-    }
-    for (int k = 0; k < 3; k++) fclose(fp[k]);
-    free(host);
-    return rc;
 }
 
 // Developer aid: read the persistent sweep's counters on a side stream while a kernel is running.

@@ -183,6 +183,7 @@ struct nsb_ctx {
     double sor_seconds;
     long long n_launches;  // kernels of this library enqueued so far (nsb_launch_count)
     int last_sor_engine;
+    void* out_state; void* out_buffers;   // output.cu: the dump in flight (first context of a decomposition) / staging buffers
     int resident_state;    // sor_resident.cu: 0 unknown, 1 usable, -1 this device refused the cluster / cooperative launch
     char err[512];
 };
@@ -219,6 +220,10 @@ int nsb_sor_resident_supported(const nsb_ctx* c);
 cudaError_t nsb_launch_sor_resident(nsb_ctx* c, int max_it, int check);
 
 void nsb_sor_plan(nsb_ctx* c);
+// output.cu: field dumps in the reference's format for the n slabs cs[0..n-1] of one decomposition (rank order)
+int nsb_out_run(nsb_ctx** cs, int n, double t, const char* prefix, int async);
+int nsb_out_wait(nsb_ctx* c0);
+void nsb_out_release(nsb_ctx* c);
 
 // ---- slab decomposition (slab.cu / step.cu)
 SlabRed nsb_slab_red(const nsb_ctx* c);

@@ -544,6 +544,20 @@ extern "C" int nsb_group_download(nsb_group* g, int field, double* host, int lay
     return group_xfer(g, field, host, layout, false);
 }
 
+// io.h:31 output() for a decomposition: every slab contributes its rows to the same three files
+extern "C" int nsb_group_output(nsb_group* g, double t, const char* prefix) {
+    if (!g || !prefix) return NSB_ERR_ARG;
+    return nsb_out_run(g->c, g->n, t, prefix, 0);
+}
+extern "C" int nsb_group_output_async(nsb_group* g, double t, const char* prefix) {
+    if (!g || !prefix) return NSB_ERR_ARG;
+    return nsb_out_run(g->c, g->n, t, prefix, 1);
+}
+extern "C" int nsb_group_output_wait(nsb_group* g) {
+    if (!g) return NSB_ERR_ARG;
+    return nsb_out_wait(g->c[0]);
+}
+
 extern "C" int nsb_group_get_center(nsb_group* g, double* u_c, double* v_c) {
     if (!g) return NSB_ERR_ARG;
     const int jc = g->c[0]->J / 2;                              // main.c:148-149 (global row)

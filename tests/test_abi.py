@@ -127,3 +127,29 @@ def test_chunk_height_model_of_the_persistent_sweep():
             assert 16 <= r <= 128 and r % 2 == 0 and r >= prev - 12
             prev = r
     assert f(8192, 8, 1776, 1) == 16 and f(5, 250, 1776, 1) == 16 and f(100, 100, 0, 1) >= 16
+
+
+def test_output_formatter_equals_printf():
+    """output.cu formats "%.5f" in exact integer arithmetic (host code of libnsb200.so, no GPU needed): it must produce
+    printf's bytes -- round half to even on the exact binary value -- for field-like values, exact ties (k/64),
+    zeros of both signs, denormals, huge values and infinities (the reference writes with fprintf, io.c:103-112)."""
+    import ctypes as C
+    import random
+    import struct
+    L = nsb().lib()
+    f = L.nsb_debug_fmt5
+    f.restype = C.c_int
+    f.argtypes = [C.c_double, C.c_char_p]
+    buf = C.create_string_buffer(512)
+    rnd = random.Random(7)
+    vals = [0.0, -0.0, 1.0, -1.0, 0.015625, 0.046875, -0.015625, 1e-9, -1e-9, 123456789.123456, 0.999995, 0.9999949999,
+            0.000005, 5e-6, 4.9e-324, 1e-310, 7e13, 7.1e13, 1e15, 1e300, float("inf"), float("-inf"), 2.0 ** 46 - 0.001, 2.0]
+    vals += [k / 64 for k in range(-200, 200)] + [k / 128 + 1000 for k in range(100)]
+    vals += [rnd.uniform(-1, 1) * 10.0 ** rnd.choice([0, 0, 0, 1, 2, 3, -3, -5, -8, 5, 10]) for _ in range(100000)]
+    for _ in range(50000):
+        x = struct.unpack("<d", struct.pack("<Q", rnd.getrandbits(64)))[0]
+        if x == x:                       # glibc prints the sign of a NaN, python does not: NaNs go through snprintf itself
+            vals.append(x)
+    for x in vals:
+        n = f(x, buf)
+        assert buf.value.decode() == "%.5f" % x and n == len(buf.value), repr(x)

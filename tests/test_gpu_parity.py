@@ -464,6 +464,38 @@ def test_output_files_match_reference_format(tmp_path):
     s.close()
 
 
+def test_output_async_and_slabs_write_the_same_bytes(tmp_path):
+    """nsb_output_async (device snapshot, side-stream copy, host formatting threads) while the time loop goes on,
+    and nsb_group_output over 3 y-slabs: the same bytes as the oracle's writer (pinned to io.c:output) for the
+    fields AT THE TIME OF THE CALL."""
+    m = nsb()
+    kw = dict(i_max=70, j_max=48, T=1e9, a=1.0, b=0.75, max_it=60)
+    P = m.make_params(**kw)
+    (tmp_path / "a").mkdir(); (tmp_path / "o").mkdir(); (tmp_path / "g").mkdir()
+    with m.Solver(P, sor_engine=m.SOR_STREAM, chunk_rows=16) as s:
+        t = 0.0
+        for k in range(3):
+            t += s.step(t)["dt"]
+        u, v, p = s.download(m.U), s.download(m.V), s.download(m.P)
+        s.output(t, str(tmp_path / "a" / "0"), wait=False)
+        t2 = t
+        for k in range(3):                                   # the solver moves on while the dump is written
+            t2 += s.step(t2)["dt"]
+        s.output_wait()
+        assert not np.array_equal(s.download(m.U), u)
+    ob.lib().orc_output(P.i_max, P.j_max, ob._ptr(u), ob._ptr(v), ob._ptr(p), t, P.a, P.b, str(tmp_path / "o" / "0").encode())
+    with m.Group(P, [0, 0, 0], chunk_rows=16) as g:
+        tg = 0.0
+        for k in range(3):
+            tg += g.step(tg)["dt"]
+        assert tg == t
+        g.output(tg, str(tmp_path / "g" / "0"))
+    for suf in ("_u.txt", "_v.txt", "_p.txt"):
+        want = (tmp_path / "o" / ("0" + suf)).read_bytes()
+        assert (tmp_path / "a" / ("0" + suf)).read_bytes() == want
+        assert (tmp_path / "g" / ("0" + suf)).read_bytes() == want
+
+
 def test_c_driver_process_contract(tmp_path):
     """build/parallel: same stdout lines as the serial reference binary at %.6f, stderr ends with
     the SOR seconds and no newline."""
