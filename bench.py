@@ -165,9 +165,9 @@ def cpu_reference_sor(size, iters_per_step, steps, warmup):
 
 
 # ----------------------------------------------------------------------------- parity gate
-def parity_gate(m, rank, world, local, dist, ni=2048, rows_per_gpu=2048, iters=30):
+def parity_gate(m, rank, world, local, dist, pass_k, chunk_rows, ni=2048, rows_per_gpu=2048, iters=30):
     """Runs BEFORE the timed region, at every N, through the SAME engine the timing uses (persistent sweep, the
-    multi-slab kernel with in-flight halo flags at N > 1, the timed run's chunk height): one whole time step of a
+    multi-slab kernel with in-flight halo flags at N > 1, the timed run's iterations per pass and chunk height): one whole time step of a
     ni x (rows_per_gpu * N) cavity with max_it = `iters` (BC, F/G, RHS, `iters` red+black+residual iterations,
     velocity update) and `iters` more bare iterations.  Rank 0 then solves the same GLOBAL problem on one slab and
     with the CPU oracle (all host cores; the oracle is the checker, never the thing timed) and compares, bit for bit,
@@ -177,7 +177,7 @@ def parity_gate(m, rank, world, local, dist, ni=2048, rows_per_gpu=2048, iters=3
     nj = rows_per_gpu * world
     P = m.make_params(problem=1, f=1.0, i_max=ni, j_max=nj, a=1.0, b=float(nj) / float(ni), T=1.0e9, Re=1000.0,
                       g_x=0.0, g_y=0.0, tau=1.0, omega=1.7, epsilon=1e-4, max_it=iters, n_print=1)
-    ch = 128
+    ch = chunk_rows
 
     def digest(rows):           # rows: C-contiguous (n_rows, ni + 2) block, x fastest
         return hashlib.sha256(np.ascontiguousarray(rows).tobytes()).hexdigest()
@@ -196,9 +196,9 @@ def parity_gate(m, rank, world, local, dist, ni=2048, rows_per_gpu=2048, iters=3
     if world == 1:
         mine = None
     else:
-        s = m.SlabSolver(P, rank, world, m.torch_all_gather(), device=local, chunk_rows=ch)
+        s = m.SlabSolver(P, rank, world, m.torch_all_gather(), device=local, chunk_rows=ch, pass_k=pass_k)
         mine = run(s, s.j_lo, s.nj)
-        engine = "sor_persist_kernel<*, MULTI=1>, %d slabs, chunk_rows %d" % (world, s.chunk_rows)
+        engine = "sor_persist_kernel<*, MULTI=1, K=%d>, %d slabs, chunk_rows %d" % (s.sor_plan()["pass_k"], world, s.chunk_rows)
         dist.barrier()
         s.close()
         blobs = m.torch_all_gather()(json.dumps(mine).encode().ljust(1024))
@@ -206,14 +206,15 @@ def parity_gate(m, rank, world, local, dist, ni=2048, rows_per_gpu=2048, iters=3
     result = None
     if rank == 0:
         # the same global problem on ONE slab (single-slab instantiation of the same sweep)
-        with m.Solver(P, device=local, sor_engine=m.SOR_STREAM, chunk_rows=ch) as s1:
+        with m.Solver(P, device=local, sor_engine=m.SOR_STREAM, chunk_rows=ch, pass_k=pass_k) as s1:
+            k1 = s1.sor_plan()["pass_k"]
             info = s1.step(0.0)
             res2 = s1.sor_iterations(iters)
             one = {"dt": float(info["dt"]).hex(), "res": float(info["res"]).hex(), "res2": float(res2).hex(),
                    "iters": info["sor_iters"]}
             F1 = {name: s1.download(f, layout=m.LAYOUT_XFAST) for name, f in (("u", m.U), ("v", m.V), ("p", m.P))}
         if world == 1:
-            engine = "sor_persist_kernel<*, MULTI=0>, chunk_rows %d" % ch
+            engine = "sor_persist_kernel<*, MULTI=0, K=%d>, chunk_rows %d" % (k1, ch)
             parts = []
         ok_slabs = True
         for q in parts:
@@ -268,6 +269,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--engine", type=int, default=0)
     ap.add_argument("--chunk-rows", type=int, default=0)
+    ap.add_argument("--pass-k", type=int, default=0, help="SOR iterations per pass over HBM: 1, 2, or 0 = planner's choice")
     ap.add_argument("--no-parity", action="store_true", help="skip the parity gate that runs before the timed region")
     args = ap.parse_args()
 
@@ -343,26 +345,27 @@ def main():
         dist.all_reduce(tt, op=dist.ReduceOp.SUM)
         return float(tt.item())
 
+    P = m.make_params(problem=1, f=1.0, i_max=ni, j_max=nj, a=1.0, b=float(nj) / float(ni), T=1.0e9, Re=1000.0,
+                      g_x=0.0, g_y=0.0, tau=1.0, omega=1.7, epsilon=1e-4, max_it=max_it, n_print=1)
+    if world == 1:
+        s = m.Solver(P, device=local, sor_engine=args.engine, chunk_rows=args.chunk_rows, pass_k=args.pass_k)
+        nj_local = nj
+    else:
+        # one slab per process; NCCL only carries the 256-byte slab descriptors, once.
+        # 124-row bands: 124 + 11 rows are 17 blocks of 8 steps of the two-iteration pass (128 would need an 18th)
+        ch = args.chunk_rows or 124
+        s = m.SlabSolver(P, rank, world, m.torch_all_gather(), device=local, chunk_rows=ch, pass_k=args.pass_k)
+        nj_local = s.nj
+    plan = s.sor_plan()
+
     parity = {"checked": False}
     if not args.no_parity:
-        parity = parity_gate(m, rank, world, local, dist)
+        parity = parity_gate(m, rank, world, local, dist, plan["pass_k"], plan["chunk_rows"])
         if rank == 0 and not parity["ok"]:
             print(json.dumps({"metric": "sor_mlups", "value": None, "n_gpus": world, "parity": parity,
                               "error": "parity gate failed: nothing was timed"}))
             sys.exit(3)
         barrier()
-
-    P = m.make_params(problem=1, f=1.0, i_max=ni, j_max=nj, a=1.0, b=float(nj) / float(ni), T=1.0e9, Re=1000.0,
-                      g_x=0.0, g_y=0.0, tau=1.0, omega=1.7, epsilon=1e-4, max_it=max_it, n_print=1)
-    if world == 1:
-        s = m.Solver(P, device=local, sor_engine=args.engine, chunk_rows=args.chunk_rows)
-        nj_local = nj
-    else:
-        # one slab per process; NCCL only carries the 256-byte slab descriptors, once
-        # 128-row bands deal 8192 rows per GPU out evenly (120-row bands would leave one rank a band more)
-        ch = args.chunk_rows or (128 if (nj // world) % 128 == 0 else 0)
-        s = m.SlabSolver(P, rank, world, m.torch_all_gather(), device=local, chunk_rows=ch)
-        nj_local = s.nj
     cells_local = float(ni) * float(nj_local)
     stream = torch.cuda.ExternalStream(s.stream, device=torch.device("cuda", local))
 
@@ -411,19 +414,22 @@ def main():
     traffic, traffic_src = None, None
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "sor_stream_traffic.json")))
-        traffic = tj.get("dram_bytes_per_iteration") * n_k
-        traffic_src = "static, not measured in this run: " + tj.get("source", "profiles/sor_stream_traffic.json")
+        traffic = tj["dram_bytes_per_iteration"][str(plan["pass_k"])] * n_k
+        traffic_src = "static, not measured in this run: " + tj["source"][str(plan["pass_k"])]
     except Exception:
         pass
-    roofline = {"bound": "hbm", "kernel": "sor_persist_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": "sor_persist_kernel<K=%d>" % plan["pass_k"], "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic if (world == 1 and size == 8192) else None,
                 "traffic_source": traffic_src if (world == 1 and size == 8192) else None,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
-                "iterations_per_launch": n_k, "algorithmic_bytes_per_launch": 24.0 * cells_local * n_k,
+                "iterations_per_launch": n_k, "iterations_per_pass": plan["pass_k"], "chunk_rows": plan["chunk_rows"],
+                "algorithmic_bytes_per_launch": 24.0 * cells_local * n_k,
                 "launch_ms": k_ms * n_k, "ms_per_iteration": k_ms,
                 "kernel_mlups": cells_local / (k_ms * 1e-3) / 1e6,
-                "note": "per GPU: one launch = %d red+black+residual iterations over this GPU's cells "
-                        "(persistent sweep), 24 B per cell per iteration; traffic = ncu DRAM bytes per iteration" % n_k}
+                "note": "per GPU: one launch = %d red+black+residual iterations over this GPU's cells (persistent sweep, %d "
+                        "iteration(s) per pass over HBM); `achieved` counts the ALGORITHMIC 24 B per cell per iteration (p in, RHS in, "
+                        "p out), so with two iterations per pass (temporal blocking) it can exceed the HBM peak -- `traffic` = "
+                        "DRAM bytes of that launch from ncu" % (n_k, plan["pass_k"])}
 
     # ---- end to end: host grids in, host grids out, pinned host memory, copies inside the timed region
     e2e = None

@@ -86,8 +86,9 @@ typedef struct nsb_options {
     int sor_chunk_rows;  /* rows per streaming chunk (0 = auto)                                 */
     int sor_check_batch; /* SOR launches the host may run ahead of the device (0 = auto, 24)      */
     void* stream;        /* cudaStream_t to run on (NULL = library creates its own)              */
-    int sor_pass_k;      /* SOR iterations per pass over HBM of the persistent sweep: 0 / 1 = one, 2 = two
-                            (temporal blocking: half the DRAM traffic, same bits; environment NSB_SOR_K overrides) */
+    int sor_pass_k;      /* SOR iterations per pass over HBM of the persistent sweep: 1 = one, 2 = two (temporal
+                            blocking: half the DRAM traffic, same bits), 0 = chosen by the cost model (two from
+                            ~5000^2 up with power-of-two spacing); environment NSB_SOR_K overrides */
     int spin_timeout_ms; /* deadline of every in-kernel wait (flags between tasks / slabs); 0 = 2000 ms.  Raise it
                             under compute-sanitizer or ncu replay, where a kernel runs orders of magnitude slower */
     int reserved[6];
@@ -156,6 +157,8 @@ int nsb_get_center(nsb_ctx* ctx, double* u_c, double* v_c);
 double nsb_sor_seconds(const nsb_ctx* ctx);
 /* kernels this library has enqueued on the context so far (bench.py's gpu_launches) */
 long long nsb_launch_count(const nsb_ctx* ctx);
+/* what the planner chose for the persistent SOR sweep: iterations per pass (1 / 2), rows per chunk, strips, chunks */
+int nsb_sor_plan_info(const nsb_ctx* ctx, int* pass_k, int* chunk_rows, int* n_strips, int* n_chunks);
 
 /* host <-> HBM.  host holds (i_max+2)*(j_max+2) doubles in the given layout. */
 int nsb_upload(nsb_ctx* ctx, int field, const double* host, int layout);

@@ -106,6 +106,7 @@ ABI = {
     "nsb_get_center": (C.c_int, [C.c_void_p, dbl_p, dbl_p]),
     "nsb_sor_seconds": (C.c_double, [C.c_void_p]),
     "nsb_launch_count": (C.c_longlong, [C.c_void_p]),
+    "nsb_sor_plan_info": (C.c_int, [C.c_void_p, int_p, int_p, int_p, int_p]),
     "nsb_upload": (C.c_int, [C.c_void_p, C.c_int, dbl_p, C.c_int]),
     "nsb_download": (C.c_int, [C.c_void_p, C.c_int, dbl_p, C.c_int]),
     "nsb_output": (C.c_int, [C.c_void_p, C.c_double, C.c_char_p]),
@@ -302,6 +303,12 @@ class Solver:
 
     def launch_count(self):
         return self._L.nsb_launch_count(self._h)
+
+    def sor_plan(self) -> dict:
+        """Iterations per pass, rows per chunk, strips and chunks of the persistent SOR sweep as planned."""
+        v = [C.c_int() for _ in range(4)]
+        self._ck(self._L.nsb_sor_plan_info(self._h, *[C.byref(x) for x in v]))
+        return dict(zip(("pass_k", "chunk_rows", "n_strips", "n_chunks"), (x.value for x in v)))
 
     def output(self, t, prefix, wait=True):
         """io.h:31 output(); wait=False: returns once the fields are snapshotted, output_wait() joins the writer."""

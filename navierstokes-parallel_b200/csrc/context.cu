@@ -108,9 +108,16 @@ extern "C" int nsb_slab_partition(int j_max, int chunk_rows, int world, int rank
     if (j_max < 1 || chunk_rows < 2 || (chunk_rows & 1) || world < 1 || rank < 0 || rank >= world) return NSB_ERR_ARG;
     const int nb = (j_max + chunk_rows - 1) / chunk_rows;
     if (nb < world) return NSB_ERR_ARG;
-    const int base = nb / world, rem = nb % world;
+    // Whole bands per rank.  The FULL bands are dealt out evenly (the first `rem` ranks hold one more); a ragged last
+    // band goes to the last rank on top of its share when that rank is not one of those -- 8192 x 2 rows in 124-row
+    // bands: 66 + (66 + 16 rows) instead of 67 + (65 + 16 rows).
+    const int nfull = j_max / chunk_rows, ragged = nb - nfull;
+    int base = nb / world, rem = nb % world;
+    if (ragged && nfull >= world && (nfull % world) != 0) { base = nfull / world; rem = nfull % world; }
+    else if (ragged && nfull >= world) { base = nfull / world; rem = 0; }
+    const bool tail_extra = ragged && nfull >= world;           // the ragged band is an extra of the last rank
     const int b0 = rank * base + (rank < rem ? rank : rem);
-    const int nbr = base + (rank < rem ? 1 : 0);
+    const int nbr = base + (rank < rem ? 1 : 0) + ((tail_extra && rank == world - 1) ? 1 : 0);
     const int lo = b0 * chunk_rows;
     int hi = (b0 + nbr) * chunk_rows;
     if (hi > j_max) hi = j_max;
@@ -170,7 +177,7 @@ int nsb_create_slab_internal(const nsb_params* P, const nsb_options* opt, int ra
         c->g.nj = P->j_max; c->j_lo = 0;
     } else {
         // the chunk height is part of the decomposition: fixed before the rows are dealt out
-        int ch = c->O.sor_chunk_rows > 0 ? ((c->O.sor_chunk_rows + 1) & ~1) : 120;
+        int ch = c->O.sor_chunk_rows > 0 ? ((c->O.sor_chunk_rows + 1) & ~1) : 124;   // 124 + 11 rows = 17 blocks of the two-iteration pass
         if (ch < 16) ch = 16;
         c->O.sor_chunk_rows = ch;
         int nj = 0;
@@ -303,6 +310,16 @@ extern "C" void* nsb_stream(const nsb_ctx* c) { return c ? (void*)c->stream : NU
 extern "C" double nsb_sor_seconds(const nsb_ctx* c) { return c ? c->sor_seconds : 0.0; }
 
 extern "C" long long nsb_launch_count(const nsb_ctx* c) { return c ? c->n_launches : 0; }
+
+// What nsb_sor_plan decided for the persistent sweep of this context.
+extern "C" int nsb_sor_plan_info(const nsb_ctx* c, int* pass_k, int* chunk_rows, int* n_strips, int* n_chunks) {
+    if (!c) return NSB_ERR_ARG;
+    if (pass_k) *pass_k = nsb_sor_pass_k(c);
+    if (chunk_rows) *chunk_rows = c->chunk_rows;
+    if (n_strips) *n_strips = c->n_strips;
+    if (n_chunks) *n_chunks = c->n_chunks;
+    return NSB_OK;
+}
 
 // u and v at (i, local row l)
 int nsb_get_value(nsb_ctx* c, int i, int l, double* u_c, double* v_c) {

@@ -173,6 +173,7 @@ struct nsb_ctx {
     int st_k, st_passes, st_tail, st_buf0;   // what the last persistent solve enqueued (nsb_ph_sor_end settles the buffers)
     unsigned long long flag_base;
     int chunk_rows, n_strips, n_chunks;
+    int sor_k;             // iterations per pass of the persistent sweep as planned (nsb_sor_plan)
     // step reductions
     StepRed* d_red; StepRed* h_red;
     double* d_red_partials; int n_red_partials;
@@ -211,6 +212,7 @@ cudaError_t nsb_launch_sor_lex(nsb_ctx* c, int max_it, int check);       // seri
 cudaError_t nsb_launch_sor_simple_iter(nsb_ctx* c, int it, double* p, int check);
 extern "C" int nsb_plan_chunk_rows(int ni, int nj, long long slots, int recip);   // sor_stream.cu, host arithmetic
 extern "C" int nsb_plan_chunk_rows_k(int ni, int nj, long long slots, int recip, int k);
+extern "C" int nsb_plan_sor(int ni, int nj, long long slots1, long long slots2, int recip, int* rows);
 SorCoef nsb_make_sor_coef(nsb_ctx* c, long long cells);                  // sor_simple.cu; cells = GLOBAL i_max * j_max
 cudaError_t nsb_launch_sor_finish_ghosts(nsb_ctx* c, double* pfinal, const double* pprev);
 cudaError_t nsb_launch_to_xfast(nsb_ctx* c, const double* src_ref, double* dst);   // [i][j] -> grid

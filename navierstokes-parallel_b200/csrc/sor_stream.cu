@@ -76,6 +76,25 @@ static_assert(SOR_BLK % (2 * SOR_NST) == 0, "SOR_BLK must be a multiple of 2 * S
 // step and its south neighbour (lag L+1) not yet -- exactly the state the reference's sequence
 // (ghosts, colour 0, ghosts, colour 1, residual; main.cu:684-706) produces row by row.  K = 2 needs rows
 // j .. j-7 in the window: the 8 slots the unrolled block has anyway.
+// How strips that reach beyond the interior columns are handled when every lane is entirely inside or entirely
+// outside the domain (i_max a multiple of 4): 0 = by the general per-column edge body like any other edge strip,
+// 1 = by the plain bodies with a per-lane mask evaluated at run time (one body for all strips),
+// 2 = by separate masked instantiations of the plain bodies (interior strips carry no mask code).
+// The general edge body costs ~3 x the plain one per row, and the edge tasks of pass n+1 wait for the edge tasks of
+// pass n: they are the critical path of every pass whenever there is less than ~2.5 tasks per resident warp.
+// Which mode is fastest depends on what it does to the register allocation and the instruction footprint of each
+// instantiation -- measured on one B200 in one run (profiles/r2m_variants.txt, us per iteration, modes 0 / 1 / 2):
+//   one iteration per pass, reciprocal product: 2048^2 36.6 / 32.2 / 42.4   4096^2 77.2 / 75.4 / 89.6   8192^2 250.3 / 253.5 / 253.2
+//   one iteration per pass, IEEE division 8191^2: 309.8 / 383.1 / 431.8      (mode 2 spills in the plain body)
+//   two iterations per pass, 8192^2: 248.0 / 299.3 / 193.3                   (its edge body is ~100 KB: mode 0 runs at ITS pace)
+// hence: two iterations per pass -> 2; reciprocal product -> 1; IEEE division -> 0.  -DSOR_LANEMASK_MODE=n forces one.
+__host__ __device__ constexpr int sor_lanemask_mode(int qm, int k) {
+#ifdef SOR_LANEMASK_MODE
+    return SOR_LANEMASK_MODE;
+#else
+    return k >= 2 ? 2 : (qm == NSB_QUOT_RECIP ? 1 : 0);
+#endif
+}
 template <int K>
 struct SorK {
     static constexpr int HALO = 2 * K + 1;        // rows a task reads below its first / above its last row; rows pushed across a slab boundary
@@ -177,6 +196,9 @@ __device__ __forceinline__ void sor_close_iteration(double total, SorCtl* ctl, i
 // Per-lane geometry, fixed for the whole task.
 struct LaneGeom {
     bool inner[4];   // column k is an interior column (1 <= i <= i_max)
+    bool li;         // all four columns of this lane are interior columns
+    bool masked;     // warp-uniform: the strip holds ghost / pad columns AND every lane is either all-interior or
+                     // all-exterior (i_max a multiple of 4): the plain bodies handle it with the per-lane mask `li`
     bool owner;      // lanes 1..30 with an in-bounds group: stores and residual
     bool ghostW;     // this lane's column 3 is the west ghost column i = 0
     int kGhostE;     // column of this lane that is the east ghost i = i_max+1, or -1
@@ -273,7 +295,7 @@ __device__ __forceinline__ void issue_pair(TaskCtx& t, int st, uint32_t empty_ph
 //       is USED left the window of the three-operation division (pad / ghost columns of an edge strip may
 //       hold anything and are not counted).
 // The last black phase (L = 3K-1) leaves the row final and stores it (one full 32-byte sector per lane).
-template <int QM, bool EX, bool EY, int K, int S, int L>
+template <int QM, bool EX, bool EY, bool MASK, int K, int S, int L>
 __device__ __forceinline__ void sor_colour(double (&P)[SOR_BLK][4], double (&R)[SOR_BLK][4], const int j, TaskCtx& t,
                                            const SorCoef& kf, const LaneGeom& lg, bool& ok) {
     constexpr int NS = SOR_BLK;
@@ -292,7 +314,9 @@ __device__ __forceinline__ void sor_colour(double (&P)[SOR_BLK][4], double (&R)[
     const int r = j - L;
     const bool row_in = !EY || ((r >= (t.wall_bottom ? 1 : -margin)) && (r <= (t.wall_top ? t.nj : t.nj + 1 + margin)));
     double (&X)[4] = P[sX];
-    if (EX) refresh_ghost_columns(X, lg);                               // main.cu:686 / 694
+    constexpr int LM = sor_lanemask_mode(QM, K);
+    const bool mask = MASK || (LM == 1 && !EX && lg.masked);
+    if (EX || mask) refresh_ghost_columns(X, lg);                       // main.cu:686 / 694
     if (EY) {
         if (r == 1 && t.wall_bottom) {
 #pragma unroll
@@ -317,11 +341,17 @@ __device__ __forceinline__ void sor_colour(double (&P)[SOR_BLK][4], double (&R)[
     bool ok0 = true, ok1 = true;
     const double u0 = sor_cell_q<QM>(X[c0], e0, w0, P[sN][c0], P[sS][c0], R[sX][c0], kf, EX ? ok0 : ok);
     const double u1 = sor_cell_q<QM>(X[c1], e1, w1, P[sN][c1], P[sS][c1], R[sX][c1], kf, EX ? ok1 : ok);
-    if (row_in && (!EX || lg.inner[c0])) { X[c0] = u0; if (EX) ok = ok && ok0; }
-    if (row_in && (!EX || lg.inner[c1])) { X[c1] = u1; if (EX) ok = ok && ok1; }
+    if (EX) {
+        if (row_in && lg.inner[c0]) { X[c0] = u0; ok = ok && ok0; }
+        if (row_in && lg.inner[c1]) { X[c1] = u1; ok = ok && ok1; }
+    } else {
+        // MASK: lanes outside the domain (first / last strip of a grid whose i_max is a multiple of 4) keep
+        // their values -- a per-lane select instead of the per-column predicates of the general edge body
+        if (row_in && (!(MASK || LM == 1) || lg.li)) { X[c0] = u0; X[c1] = u1; }    // (pad lanes' `ok` is discarded at the end of the task)
+    }
     if (STORE) {
         const bool in_chunk = (r >= t.jc0 && r <= t.jc1);     // warp-uniform; the blocks at the ends of a chunk run this body too
-        if (EX && in_chunk) {
+        if ((EX || mask) && in_chunk) {
             // ghost columns of the final row, as the refresh before colour 1 left them (main.cu:694):
             // the west ghost lives in the halo lane 0 of the first strip, the east ghost in an owner
             // lane (stored below with its group) or in the halo lane 31 of the last strip
@@ -370,7 +400,7 @@ __device__ __forceinline__ void sor_colour(double (&P)[SOR_BLK][4], double (&R)[
 
 // ---- residual of row j - L (final for its sub-iteration, as are its neighbours) with the ghosts as they are
 //      (last refreshed before colour 1, main.cu:694-702)
-template <int QM, bool EX, bool EY, int S, int L>
+template <int QM, bool EX, bool EY, bool MASK, int K, int S, int L>
 __device__ __forceinline__ void sor_resid(double (&P)[SOR_BLK][4], double (&R)[SOR_BLK][4], const int j, const TaskCtx& t,
                                           const SorCoef& kf, const LaneGeom& lg, double& acc, bool& ok) {
     constexpr int NS = SOR_BLK;
@@ -390,26 +420,27 @@ __device__ __forceinline__ void sor_resid(double (&P)[SOR_BLK][4], double (&R)[S
             const double q = sor_residual_q<QM>(X[k], e, w, P[sN][k], P[sS][k], R[sX][k], kf, EX ? okr : ok);
             if (!EX || lg.inner[k]) { part = fma(q, q, part); if (EX) ok = ok && okr; }
         }
+        if ((MASK || (sor_lanemask_mode(QM, K) == 1 && !EX)) && !lg.li) part = 0.0;        // lanes outside the domain (masked strips)
         acc += part;                           // non-owner lanes are discarded at the end of the task
     }
 }
 
 // the three phases of sub-iteration Q, then those of Q + 1
-template <int QM, bool EX, bool EY, int K, int S, int Q>
+template <int QM, bool EX, bool EY, bool MASK, int K, int S, int Q>
 __device__ __forceinline__ void sor_phases(double (&P)[SOR_BLK][4], double (&R)[SOR_BLK][4], const int j, TaskCtx& t,
                                            const SorCoef& kf, const LaneGeom& lg, double (&acc)[K], bool& ok) {
     if constexpr (Q < K) {
-        sor_colour<QM, EX, EY, K, S, 3 * Q + 1>(P, R, j, t, kf, lg, ok);
-        sor_colour<QM, EX, EY, K, S, 3 * Q + 2>(P, R, j, t, kf, lg, ok);
-        sor_resid<QM, EX, EY, S, 3 * Q + 3>(P, R, j, t, kf, lg, acc[Q], ok);
-        sor_phases<QM, EX, EY, K, S, Q + 1>(P, R, j, t, kf, lg, acc, ok);
+        sor_colour<QM, EX, EY, MASK, K, S, 3 * Q + 1>(P, R, j, t, kf, lg, ok);
+        sor_colour<QM, EX, EY, MASK, K, S, 3 * Q + 2>(P, R, j, t, kf, lg, ok);
+        sor_resid<QM, EX, EY, MASK, K, S, 3 * Q + 3>(P, R, j, t, kf, lg, acc[Q], ok);
+        sor_phases<QM, EX, EY, MASK, K, S, Q + 1>(P, R, j, t, kf, lg, acc, ok);
     }
 }
 
 // One pipeline step with compile-time window slot S (row parity == S parity).  sb is the step
 // number of the first step of the current block of 8 (a multiple of 8); the row that arrives in
 // this step is j = jstart + sb + S.
-template <int QM, bool EX, bool EY, int K, int S>
+template <int QM, bool EX, bool EY, bool MASK, int K, int S>
 __device__ __forceinline__ void sor_step(double (&P)[SOR_BLK][4], double (&R)[SOR_BLK][4], const int sb, const uint32_t use0, TaskCtx& t,
                                          const SorCoef& kf, const LaneGeom& lg, double (&acc)[K], bool& ok) {
     constexpr int NS = SOR_BLK;                                                    // window slots
@@ -461,23 +492,23 @@ __device__ __forceinline__ void sor_step(double (&P)[SOR_BLK][4], double (&R)[SO
             issue_pair<K>(t, st, ph ^ t.empty_par, true);
         }
     }
-    sor_phases<QM, EX, EY, K, S, 0>(P, R, j, t, kf, lg, acc, ok);
+    sor_phases<QM, EX, EY, MASK, K, S, 0>(P, R, j, t, kf, lg, acc, ok);
     if (K > 1) t.ex = ex_new;                 // used by the red update of this row in the next step
 }
 
-template <int QM, bool EX, bool EY, int K, int S>
+template <int QM, bool EX, bool EY, bool MASK, int K, int S>
 __device__ __forceinline__ void sor_steps_from(double (&P)[SOR_BLK][4], double (&R)[SOR_BLK][4], const int sb, const uint32_t use0,
                                                TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, double (&acc)[K], bool& ok) {
     if constexpr (S < SOR_BLK) {
-        sor_step<QM, EX, EY, K, S>(P, R, sb, use0, t, kf, lg, acc, ok);
-        sor_steps_from<QM, EX, EY, K, S + 1>(P, R, sb, use0, t, kf, lg, acc, ok);
+        sor_step<QM, EX, EY, MASK, K, S>(P, R, sb, use0, t, kf, lg, acc, ok);
+        sor_steps_from<QM, EX, EY, MASK, K, S + 1>(P, R, sb, use0, t, kf, lg, acc, ok);
     }
 }
 // One unrolled block of SOR_BLK steps; use0 = times every ring stage has been used before this block.
-template <int QM, bool EX, bool EY, int K>
+template <int QM, bool EX, bool EY, bool MASK, int K>
 __device__ __forceinline__ void sor_block8(double (&P)[SOR_BLK][4], double (&R)[SOR_BLK][4], const int sb, const uint32_t use0,
                                            TaskCtx& t, const SorCoef& kf, const LaneGeom& lg, double (&acc)[K], bool& ok) {
-    sor_steps_from<QM, EX, EY, K, 0>(P, R, sb, use0, t, kf, lg, acc, ok);
+    sor_steps_from<QM, EX, EY, MASK, K, 0>(P, R, sb, use0, t, kf, lg, acc, ok);
 }
 
 // Steps of a task: rows jstart .. jc1 + 3K arrive (the last ones only to drain the pipeline: the last residual of
@@ -515,14 +546,22 @@ __device__ __forceinline__ void sor_run_task(TaskCtx& t, const SorCoef& kf, cons
 #endif
         // (a fourth variant <EX, !EY> for the interior rows of the two edge strips was measured: the larger
         //  kernel body costs the LEAN path 10 % -- 5.27 against 5.86 TB/s at 8192^2 -- and was dropped)
-        if (EX) sor_block8<QM, true, true, K>(P, R, sb, use0, t, kf, lg, acc, ok);
-        else if (clean && QM != NSB_QUOT_FULL) sor_block8<QM, false, false, K>(P, R, sb, use0, t, kf, lg, acc, ok);
-        else sor_block8<QM, false, true, K>(P, R, sb, use0, t, kf, lg, acc, ok);
+        // Five bodies: the general edge body (per-column predicates), and plain / wall bodies with and without the
+        // per-lane mask.  Interior strips -- all but two -- only ever run the two unmasked ones.
+        if (EX) sor_block8<QM, true, true, false, K>(P, R, sb, use0, t, kf, lg, acc, ok);
+        else if (sor_lanemask_mode(QM, K) == 2 && lg.masked) {
+            if (clean && QM != NSB_QUOT_FULL) sor_block8<QM, false, false, true, K>(P, R, sb, use0, t, kf, lg, acc, ok);
+            else sor_block8<QM, false, true, true, K>(P, R, sb, use0, t, kf, lg, acc, ok);
+        } else {
+            if (clean && QM != NSB_QUOT_FULL) sor_block8<QM, false, false, false, K>(P, R, sb, use0, t, kf, lg, acc, ok);
+            else sor_block8<QM, false, true, false, K>(P, R, sb, use0, t, kf, lg, acc, ok);
+        }
     }
     if (!lg.owner) {
 #pragma unroll
         for (int q = 0; q < K; q++) acc[q] = 0.0;
     }
+    if (!EX && lg.masked && !lg.li) ok = true; // quotients of lanes outside the domain are never used: they may hold anything
 }
 
 // Phase parities of a warp's mbarriers after one task of n_steps rows (see sor_persist_kernel).
@@ -566,7 +605,7 @@ __device__ __forceinline__ void sor_task(TaskCtx& t, const SorCoef& kf, const La
 
 // Geometry of one task (strip, chunk) for a pass of K sub-iterations: everything of TaskCtx that does not depend on
 // the buffers.  MULTI: several y-slabs.
-template <bool MULTI, int K>
+template <bool RECIP, bool MULTI, int K>
 __device__ __forceinline__ void sor_task_geometry(TaskCtx& t, LaneGeom& lg, bool& edge_strip, const SorStreamArgs& a,
                                                   int strip, int chunk, int lane) {
     constexpr int HALO = SorK<K>::HALO;
@@ -574,22 +613,34 @@ __device__ __forceinline__ void sor_task_geometry(TaskCtx& t, LaneGeom& lg, bool
     const int g0 = strip * NSB_STRIP_GROUPS;             // first column group of the strip
     const int g = g0 + lane;                             // column group of this lane
     const int i0 = g * NSB_GROUP - NSB_COL0;             // i of column k = 0
-    bool all_inner = (g < a.n_groups);
+    bool all_inner = (g < a.n_groups), none_inner = true;
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         lg.inner[k] = (i0 + k >= 1) && (i0 + k <= a.ni);
         all_inner = all_inner && lg.inner[k];
+        none_inner = none_inner && !lg.inner[k];
     }
+    lg.li = all_inner;
     lg.owner = (g < a.n_groups) && lane >= 1 && lane <= NSB_STRIP_GROUPS;
     lg.ghostW = (i0 + 3 == 0);
     const int kg = a.ni + 1 - i0;
     lg.kGhostE = (kg >= 0 && kg <= 3) ? kg : -1;
     lg.warpW = __any_sync(FULLM, lg.ghostW);
     lg.warpE = __any_sync(FULLM, lg.kGhostE >= 0);
+    // Strips that reach beyond the interior columns: when every lane is entirely inside or entirely outside
+    // (i_max a multiple of 4: the west ghost is the last column of lane 0, the east ghost the first column of its
+    // lane) the plain bodies handle them with a per-lane mask; only otherwise the general per-column edge body runs.
+    // (The edge body costs ~3 x the plain one per row and sits on the critical path of every iteration: the edge
+    // tasks of iteration n+1 wait for the edge tasks of iteration n.  2048^2 .. 4096^2 ran at exactly their pace.)
+    const bool any_out = !__all_sync(FULLM, all_inner);
+    const bool uniform = __all_sync(FULLM, all_inner || none_inner || g >= a.n_groups);
 #ifdef SOR_FORCE_EX
     edge_strip = true;
+    lg.masked = false;
 #else
-    edge_strip = !__all_sync(FULLM, all_inner);
+    constexpr int LM = sor_lanemask_mode(RECIP ? NSB_QUOT_RECIP : NSB_QUOT_TRY, K);
+    edge_strip = LM == 0 ? any_out : (any_out && !uniform);
+    lg.masked = LM != 0 && any_out && uniform;
 #endif
     t.jc0 = 1 + chunk * a.chunk_rows;
     t.jc1 = min(t.jc0 + a.chunk_rows - 1, a.nj);
@@ -654,7 +705,7 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
         LaneGeom lg;
         TaskCtx t;
         bool edge_strip;
-        sor_task_geometry<MULTI, 1>(t, lg, edge_strip, a, strip, chunk, lane);
+        sor_task_geometry<RECIP, MULTI, 1>(t, lg, edge_strip, a, strip, chunk, lane);
         t.full_par = 0u; t.empty_par = 0u;
         sor_task_buffers<1>(t, a.pin, a.pout, a.rhs, a.down_pout, a.up_pout, strip, lane);
         unsigned char* ring = smem_raw + warp * SOR_WARP_SMEM(1);
@@ -899,7 +950,7 @@ __global__ void __launch_bounds__(SOR_THREADS, (K == 1 ? SOR_MIN_BLOCKS : SOR_MI
         LaneGeom lg;
         TaskCtx t;
         bool edge_strip;
-        sor_task_geometry<MULTI, K>(t, lg, edge_strip, a, strip, chunk, lane);
+        sor_task_geometry<RECIP, MULTI, K>(t, lg, edge_strip, a, strip, chunk, lane);
         sor_task_buffers<K>(t, pa.own_p[bi], pa.own_p[bo], a.rhs, pa.down_p[bo], pa.up_p[bo], strip, lane);
         t.lds_lane = reinterpret_cast<const double*>(ring) + lane * NSB_GROUP;
         t.smem_base = smem_u32(ring);
@@ -1021,19 +1072,11 @@ int nsb_sor_persist_supported(const nsb_ctx* c) {
     return c->world == 1 || (c->connected && c->peers_distinct);
 }
 
-// Sub-iterations per pass of the persistent sweep for this context.  Default 1: on a B200 the two-iteration pass
-// halves the DRAM traffic (0.855 GB instead of 1.676 GB per iteration at 8192^2, ncu) but is not faster -- the sweep
-// is bound by instruction latency, not by HBM, once the reads are halved (255.6 us against 250.7 us per iteration,
-// profiles/r2c_*) -- so it is there on request: NSB_SOR_K=2 or nsb_options.sor_pass_k = 2.
-// Falls back to 1 where the chunks or the slab are too short for the 5-row halo.
-static int sor_k_wanted(const nsb_ctx* c) {
-    int k = c->O.sor_pass_k >= 1 && c->O.sor_pass_k <= NSB_SOR_KMAX ? c->O.sor_pass_k : 1;
-    const char* env = getenv("NSB_SOR_K");
-    if (env && atoi(env) >= 1 && atoi(env) <= NSB_SOR_KMAX) k = atoi(env);
-    return k;
-}
+// Sub-iterations per pass of the persistent sweep for this context: nsb_sor_plan decided (c->sor_k; nsb_options.sor_pass_k
+// 1 / 2 or NSB_SOR_K force it, 0 = by the cost model).  Falls back to 1 where the chunks or the slab are too short for
+// the 5-row halo.
 int nsb_sor_pass_k(const nsb_ctx* c) {
-    int k = sor_k_wanted(c);
+    int k = c->sor_k >= 1 && c->sor_k <= NSB_SOR_KMAX ? c->sor_k : 1;
     if (c->chunk_rows < 2 * SorK<2>::HALO) k = 1;
     if (c->world > 1 && c->g.nj < 2 * SorK<2>::HALO) k = 1;
     return k;
@@ -1060,36 +1103,57 @@ cudaError_t nsb_launch_sor_close(nsb_ctx* c, int it, int check) {
 
 // Chunk height of the persistent sweep (pure host arithmetic, also exported for the CPU tests):
 // `slots` = resident warps of the sweep kernel on the device, recip = reciprocal-product arithmetic,
-// k = sub-iterations per pass.
-extern "C" int nsb_plan_chunk_rows_k(int ni, int nj, long long slots, int recip, int k) {
+// k = sub-iterations per pass.  *cost_out = modelled cost of ONE PASS in step units (see nsb_plan_sor).
+static int plan_chunk_rows(int ni, int nj, long long slots, int recip, int k, double* cost_out) {
     const long long n_strips = (ni + NSB_STRIP_COLS - 1) / NSB_STRIP_COLS;
     if (slots < 1) slots = 1;
-    int best = 16;
+    int best = 10;
     double best_cost = 1e300;
-    // Chunk height of the persistent sweep, 16 .. 128 rows: minimise
-    //     max(tasks per resident warp and pass, floor) x (rows + 18),   floor = 1.6
-    // -- a task costs its rows plus ~18 row-steps of overhead (3 + 3 halo rows, 8 steps of pipeline
-    // fill, claim / flag waits; 5 + 5 halo rows and 3 more steps of drain with k = 2), and below ~1.6 tasks per warp
-    // there is nothing to overlap the dependency waits between two passes with (4096^2: 50 chunks of 82 rows = one task
-    // per warp 110 us per iteration, 86 chunks of 48 rows 90 us).  Above 128 rows the tail of a launch and the
-    // balance between SMs suffer (8192^2: 240 rows 298 us, 128 rows 265 us).  Measured optima
-    // (profiles/r1h_chunk_sweep2.txt): 2048^2 16-24, 3072^2 32, 4096^2 48, 5120^2 48-80, 6144^2 64-112,
-    // 7168^2 96-104, 8192^2 120-128; the model picks 16, 28, 50, 78, 112, 128, 128.
-    // With the IEEE division the sweep is instruction bound instead of HBM bound and the balance between
-    // warps counts for more: the measured optima sit at ~2.7 tasks per warp (4096^2 32-48 rows, 5120^2 48,
-    // 6144^2 64-80, 7168^2 90, 8191^2 112; profiles/r1h_chunk_sweep2.txt), hence the higher floor.
-    const double floor_tasks = recip ? 1.6 : 2.6;
-    const int overhead = k >= 2 ? 25 : 18;
-    for (int rows = 16; rows <= 128; rows += 2) {
+    // A task costs its blocks of 8 steps (rows + halo + drain, rounded up) plus `fill` steps of claim / flag / pipeline-fill
+    // latency; an iteration (pass) costs the tasks per resident warp times that, but never less than `floor` tasks:
+    // below it there is nothing to overlap the dependency waits between two passes with.
+    //   k = 1, reciprocal product (profiles/r2j_chunk_sweep.txt): floor 1.6, fill 12; when ONE wave of warps covers an
+    //     iteration (<= 1 task per warp) the latencies are exposed (factor 1.25).  Measured optima / picks, rows:
+    //     1024^2 10 / 10, 2048^2 26 / 22, 3072^2 34 / 26, 4096^2 50 / 50, 5120^2 66-98 / 74, 6144^2 114-128 / 106, 8192^2 128 / 128.
+    //   k = 1, IEEE division (instruction bound, the balance between warps counts for more; profiles/r1h_chunk_sweep2.txt):
+    //     floor 2.6 -- 4096^2 32-48 rows, 5120^2 48, 6144^2 64-80, 7168^2 90, 8191^2 112.
+    //   k = 2 (profiles/r2n_k2_sweep.txt; 8 resident warps per SM instead of 12): floor 3.6, fill 19, at most 124 rows
+    //     (128 rows + 11 need an 18th block).  Optima / picks: 4096^2 44 / 36, 5120^2 60 / 52, 6144^2 60-76 / 76,
+    //     7168^2 92 / 92, 8192^2 116-124 / 124, 16384^2 124 / 124.
+    const double floor_tasks = k >= 2 ? 3.6 : (recip ? 1.6 : 2.6);
+    const int fill = k >= 2 ? 19 : 12;
+    const int drain = 3 * (k >= 2 ? 2 : 1) + (2 * (k >= 2 ? 2 : 1) + 1);        // last residual lag + halo rows below
+    const int rows_max = k >= 2 ? 124 : 128;
+    for (int rows = 10; rows <= rows_max; rows += 2) {
         const long long chunks = (nj + rows - 1) / rows;
         const double per_warp = (double)(chunks * n_strips) / (double)slots;
-        const double cost = (per_warp > floor_tasks ? per_warp : floor_tasks) * (rows + overhead);
+        const int steps = (rows + drain + SOR_BLK - 1) / SOR_BLK * SOR_BLK + fill;
+        double a = per_warp > floor_tasks ? per_warp : floor_tasks;
+        if (k == 1 && recip && per_warp <= 1.0) a = 1.25;
+        const double cost = a * steps;
         if (cost < best_cost - 1e-9) { best_cost = cost; best = rows; }
         if (rows >= nj) break;
     }
+    if (cost_out) *cost_out = best_cost;
     return best;
 }
-extern "C" int nsb_plan_chunk_rows(int ni, int nj, long long slots, int recip) { return nsb_plan_chunk_rows_k(ni, nj, slots, recip, 1); }
+extern "C" int nsb_plan_chunk_rows_k(int ni, int nj, long long slots, int recip, int k) { return plan_chunk_rows(ni, nj, slots, recip, k, NULL); }
+extern "C" int nsb_plan_chunk_rows(int ni, int nj, long long slots, int recip) { return plan_chunk_rows(ni, nj, slots, recip, 1, NULL); }
+
+// Iterations per pass AND chunk height: the two-iteration pass halves the DRAM traffic but runs 8 instead of 12 warps per
+// SM and needs ~2.3 x the instructions per pass, so it wins where the one-iteration pass is HBM-bound -- from ~5000^2 up
+// (8192^2: 192 against 251 us per iteration, 16384^2: 704 against 985).  One model step costs 0.685 us with k = 1 and
+// 0.34 us per ITERATION with k = 2 (both calibrated on 4096^2 .. 8192^2, profiles/r2n_k2_sweep.txt).  IEEE division
+// (instruction-bound already) stays with one iteration per pass: 8191^2 309 against 480 us.
+// slots1 / slots2 = resident warps of the k = 1 / k = 2 kernels.  Returns k, *rows = chunk height.
+extern "C" int nsb_plan_sor(int ni, int nj, long long slots1, long long slots2, int recip, int* rows) {
+    double c1 = 0.0, c2 = 0.0;
+    const int r1 = plan_chunk_rows(ni, nj, slots1, recip, 1, &c1);
+    const int r2 = plan_chunk_rows(ni, nj, slots2, recip, 2, &c2);
+    const bool two = recip && nj >= 4 * SorK<2>::HALO && 0.34 * c2 < 0.97 * 0.685 * c1;
+    if (rows) *rows = two ? r2 : r1;
+    return two ? 2 : 1;
+}
 
 void nsb_sor_plan(nsb_ctx* c) {
     const int ni = c->g.ni, nj = c->g.nj;
@@ -1100,21 +1164,48 @@ void nsb_sor_plan(nsb_ctx* c) {
         cudaFuncSetAttribute((const void*)sor_persist_fn(v & 1, v & 2, 2), cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES(2));
     }
     c->n_strips = (ni + NSB_STRIP_COLS - 1) / NSB_STRIP_COLS;
-    const int k = sor_k_wanted(c);
-    int blocks_per_sm = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, (const void*)sor_persist_fn(c->use_recip, c->world > 1, k), SOR_THREADS,
-                                                  SOR_SMEM_BYTES(k));
-    if (blocks_per_sm < 1) blocks_per_sm = 1;
-    const long long slots = (long long)c->sm_count * blocks_per_sm * SOR_WARPS;
-    int best = 0;
-    if (c->O.sor_chunk_rows > 0) {
-        best = (c->O.sor_chunk_rows + 1) & ~1;
-    } else {
-        best = nsb_plan_chunk_rows_k(ni, nj, slots, c->use_recip ? 1 : 0, k);
+    long long slots[3] = {0, 0, 0};
+    for (int k = 1; k <= 2; k++) {
+        int bps = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (const void*)sor_persist_fn(c->use_recip, c->world > 1, k), SOR_THREADS, SOR_SMEM_BYTES(k));
+        if (bps < 1) bps = 1;
+        slots[k] = (long long)c->sm_count * bps * SOR_WARPS;
     }
-    if (best < 2) best = 2;
-    c->chunk_rows = best;
-    c->n_chunks = (nj + best - 1) / best;
+    int want = c->O.sor_pass_k >= 1 && c->O.sor_pass_k <= NSB_SOR_KMAX ? c->O.sor_pass_k : 0;      // 0 = by the model
+    {
+        const char* env = getenv("NSB_SOR_K");
+        if (env && atoi(env) >= 1 && atoi(env) <= NSB_SOR_KMAX) want = atoi(env);
+    }
+    int rows = 0, k = want;
+    if (c->O.sor_chunk_rows > 0) {
+        rows = (c->O.sor_chunk_rows + 1) & ~1;
+        // the caller fixed the chunk height (y-slabs: it is part of the decomposition): choose k for THAT height.
+        // Every rank of a decomposition must decide alike: the inputs are the bands of the LARGEST slab (ranks
+        // 0 .. rem-1 hold one band more) and the rows of the SMALLEST (the ragged last band may leave a few rows only).
+        if (k == 0) {
+            const long long bands = ((long long)c->J + rows - 1) / rows;
+            const long long bands_rank = (bands + c->world - 1) / c->world;
+            const long long tasks = (long long)c->n_strips * bands_rank;
+            k = (c->use_recip && rows >= 64 && (double)tasks / (double)slots[2] >= 3.0) ? 2 : 1;
+        }
+    } else if (k == 0) {
+        k = nsb_plan_sor(ni, nj, slots[1], slots[2], c->use_recip ? 1 : 0, &rows);
+    } else {
+        rows = plan_chunk_rows(ni, nj, slots[k], c->use_recip ? 1 : 0, k, NULL);
+    }
+    if (rows < 2) rows = 2;
+    if (c->world > 1 && k > 1) {
+        // two iterations per pass push 5 halo rows: every slab must own at least twice that
+        int min_nj = c->g.nj;
+        for (int r = 0; r < c->world; r++) {
+            int nj_r = 0;
+            if (nsb_slab_partition(c->J, rows, c->world, r, NULL, &nj_r, NULL, NULL) == NSB_OK && nj_r < min_nj) min_nj = nj_r;
+        }
+        if (min_nj < 2 * SorK<2>::HALO) k = 1;
+    }
+    c->sor_k = k;
+    c->chunk_rows = rows;
+    c->n_chunks = (nj + rows - 1) / rows;
     c->n_partials = c->n_chunks * c->n_strips;
 }
 
@@ -1216,7 +1307,8 @@ cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int k, int n_pass, int it0, int c
     pa.flag_base = c->flag_base;
     c->flag_base += (unsigned long long)n_pass + 1ull;
     int bps = 0;
-    const SorPersistFn kern = sor_persist_fn(c->use_recip, c->world > 1, k);
+    // (developer probe NSB_DEBUG_FORCE_MULTI: the multi-slab instantiation on a single slab -- what the extra code costs without any exchange)
+    const SorPersistFn kern = sor_persist_fn(c->use_recip, c->world > 1 || getenv("NSB_DEBUG_FORCE_MULTI") != NULL, k);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (const void*)kern, SOR_THREADS, SOR_SMEM_BYTES(k));
     if (bps < 1) bps = 1;
     const long long want = ((long long)n_pass * a.n_tasks + SOR_WARPS - 1) / SOR_WARPS;

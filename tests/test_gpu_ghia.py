@@ -46,15 +46,16 @@ def centerlines(m, s, n):
 
 # measured on B200 (profiles/r1e_ghia.txt): Re=100: 64^2 0.0023 / 0.0074, 128^2 0.0043 / 0.0087;
 # Re=1000: 128^2 0.0436 / 0.0436, 256^2 0.0193 / 0.0192 (max |u - Ghia| / max |v - Ghia|).
-# The two larger runs take ~1 min each on the GPU and only run with NSB_SLOW_TESTS=1.
-CASES = [(100, 64, 20.0, 0.01, 0.015, False), (1000, 128, 60.0, 0.06, 0.06, False),
-         (100, 128, 20.0, 0.01, 0.015, True), (1000, 256, 60.0, 0.03, 0.03, True)]
+# The two larger runs take ~1 min each on the GPU; they run by default (256^2 at Re=1000 is BASELINE.json configs[1]),
+# NSB_SKIP_SLOW_TESTS=1 leaves them out.  Bands = measured difference + ~15 % margin.
+CASES = [(100, 64, 20.0, 0.01, 0.015, False), (1000, 128, 60.0, 0.05, 0.05, False),
+         (100, 128, 20.0, 0.01, 0.015, True), (1000, 256, 60.0, 0.023, 0.023, True)]
 
 
 @pytest.mark.parametrize("Re,n,T,tol_u,tol_v,slow", CASES)
 def test_centerlines_match_ghia(Re, n, T, tol_u, tol_v, slow):
-    if slow and not os.environ.get("NSB_SLOW_TESTS"):
-        pytest.skip("long run: set NSB_SLOW_TESTS=1")
+    if slow and os.environ.get("NSB_SKIP_SLOW_TESTS"):
+        pytest.skip("long run left out by NSB_SKIP_SLOW_TESTS")
     m = nsb()
     P = m.make_params(i_max=n, j_max=n, a=1.0, b=1.0, T=T, Re=float(Re), tau=0.5, omega=1.7, epsilon=1e-5, max_it=1000)
     with m.Solver(P) as s:                                    # NSB_SOR_AUTO: the cluster-resident engine at these sizes

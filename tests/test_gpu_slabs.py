@@ -71,14 +71,14 @@ def test_whole_run_equals_single_slab_and_oracle(world):
 
 
 def test_slabs_at_default_chunk_and_nonsquare_box():
-    """120-row bands (the production chunk height), ragged last band, dx != dy, gravity, oscillating lid."""
+    """124-row bands (the default chunk height of a decomposition), ragged last band, dx != dy, gravity, oscillating lid."""
     m = nsb()
     P = _params(m, i_max=130, j_max=500, a=1.0, b=2.5, T=0.2, max_it=60, problem=2, f=3.0, g_x=0.3, g_y=-0.2)
-    with m.Solver(P, sor_engine=m.SOR_STREAM, chunk_rows=120) as s:
+    with m.Solver(P, sor_engine=m.SOR_STREAM, chunk_rows=124) as s:
         log1, _ = s.run(max_steps=3)
         f1 = [s.download(f) for f in (m.U, m.V, m.P)]
     with m.Group(P, [0, 0, 0]) as g:
-        assert [x["nj"] for x in g.slabs()] == [240, 240, 20]
+        assert [x["nj"] for x in g.slabs()] == [248, 124, 128]
         logg, _ = g.run(max_steps=3)
         fg = [g.download(f) for f in (m.U, m.V, m.P)]
     assert [(x["sor_iters"], x["dt"], x["res"]) for x in logg] == [(x["sor_iters"], x["dt"], x["res"]) for x in log1]
