@@ -479,6 +479,8 @@ def main():
         el = max_over_ranks(time.perf_counter() - t0)
         e2e = {"value": float(it2) * cells / el / 1e6, "unit": "MLUPS", "h2d_bytes_per_step": bi,
                "d2h_bytes_per_step": bi, "steps": args.e2e_steps, "ms_per_step": el / args.e2e_steps * 1e3, "api": api}
+        if binding is not None:
+            e2e["host_binding_rank0"] = binding
         if world == 1:
             L.nsb_host_api_reset()
     barrier()

@@ -188,6 +188,12 @@ int nsb_create_slab_internal(const nsb_params* P, const nsb_options* opt, int ra
         }
         c->g.nj = nj;
     }
+    if (c->g.nj > 131070) {
+        // the F/G and RHS kernels put two rows per block into gridDim.y (<= 65535); larger slabs need more y-slabs
+        fail(NULL, NSB_ERR_ARG, "a slab of %d rows exceeds the 131070 rows one GPU context handles: use more slabs (NSB_GPUS / nsb_group_create)", c->g.nj);
+        nsb_destroy(c);
+        return NSB_ERR_ARG;
+    }
     c->wall_bottom = (rank == 0);
     c->wall_top = (rank == world - 1);
     // pitch: COL0 + (ni+2) columns + one spare group, rounded up to 16 doubles (128 B)
@@ -402,8 +408,12 @@ extern "C" int nsb_upload(nsb_ctx* c, int field, const double* host, int layout)
     if (!dst) return fail(c, NSB_ERR_ARG, "unknown field %d", field);
     const size_t nx = (size_t)c->g.ni + 2, ny = (size_t)c->g.nj + 2;
     if (layout == NSB_LAYOUT_XFAST) {
-        CU(c, cudaMemcpy2DAsync(dst + NSB_ROW0 * c->g.pitch + NSB_COL0, c->g.pitch * sizeof(double), host,
-                                nx * sizeof(double), nx * sizeof(double), ny, cudaMemcpyHostToDevice, c->stream));
+        // ONE contiguous transfer over PCIe into the scratch grid, then a device-side 2-D copy into the pitched field:
+        // a 2-D host copy is 8194 transfers of 64 KB, which the DMA engines of 4+ ranks copying at once serve at half
+        // the rate of a single large one (profiles/r2s_h2d_probe.txt against the r2r e2e leg)
+        CU(c, cudaMemcpyAsync(c->scratch, host, nx * ny * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaMemcpy2DAsync(dst + NSB_ROW0 * c->g.pitch + NSB_COL0, c->g.pitch * sizeof(double), c->scratch,
+                                nx * sizeof(double), nx * sizeof(double), ny, cudaMemcpyDeviceToDevice, c->stream));
     } else if (layout == NSB_LAYOUT_REF) {
         CU(c, cudaMemcpyAsync(c->scratch, host, nx * ny * sizeof(double), cudaMemcpyHostToDevice, c->stream));
         CU(c, nsb_launch_to_xfast(c, c->scratch, dst));
@@ -422,9 +432,9 @@ extern "C" int nsb_download(nsb_ctx* c, int field, double* host, int layout) {
     if (!src) return fail(c, NSB_ERR_ARG, "unknown field %d", field);
     const size_t nx = (size_t)c->g.ni + 2, ny = (size_t)c->g.nj + 2;
     if (layout == NSB_LAYOUT_XFAST) {
-        CU(c, cudaMemcpy2DAsync(host, nx * sizeof(double), src + NSB_ROW0 * c->g.pitch + NSB_COL0,
-                                c->g.pitch * sizeof(double), nx * sizeof(double), ny, cudaMemcpyDeviceToHost,
-                                c->stream));
+        CU(c, cudaMemcpy2DAsync(c->scratch, nx * sizeof(double), src + NSB_ROW0 * c->g.pitch + NSB_COL0,
+                                c->g.pitch * sizeof(double), nx * sizeof(double), ny, cudaMemcpyDeviceToDevice, c->stream));
+        CU(c, cudaMemcpyAsync(host, c->scratch, nx * ny * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     } else if (layout == NSB_LAYOUT_REF) {
         CU(c, nsb_launch_from_xfast(c, src, c->scratch));
         CU(c, cudaMemcpyAsync(host, c->scratch, nx * ny * sizeof(double), cudaMemcpyDeviceToHost, c->stream));

@@ -236,6 +236,10 @@ __device__ __forceinline__ void uv_red_store(StepRed* red, const double* out) {
     red->sum_p2 = out[2];
 }
 
+// One block per grid row (1-D grid: any number of rows), 256 threads, TWO adjacent cells per thread and pass:
+// interior column i = 1 sits on a 32-byte boundary, so cells (i, i+1) with odd i are one aligned double2 of every
+// array -- F, G, p, p one row up in, u, v out; 72 B in flight per thread and pass (r1: one cell per thread, five scalar
+// loads, a block per quarter row: 4.16 TB/s with 39 stall cycles per issue on the loads, profiles/r1j_ncu_summary.txt).
 template <bool RECIPD, bool UPDATE>
 __global__ void __launch_bounds__(256) update_uv_kernel(double* __restrict__ u, double* __restrict__ v,
                                                          const double* __restrict__ F, const double* __restrict__ G,
@@ -243,37 +247,44 @@ __global__ void __launch_bounds__(256) update_uv_kernel(double* __restrict__ u, 
                                                          int nj, MomCoef m, UvRedArgs ra) {
     __shared__ double sh[32];
     __shared__ int is_last;
-    const int j = blockIdx.y + 1;
+    const int j = blockIdx.x + 1;
     const long long ro = (long long)(j + NSB_ROW0) * pitch + NSB_COL0;
+    const bool v_row = (j <= ra.v_hi);                           // global j <= j_max-1 (main.c:134)
     double mu = -1.0e300, mv = -1.0e300, sp = 0.0;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x + 1; i <= ni; i += gridDim.x * blockDim.x) {
+#pragma unroll 2
+    for (int i = 1 + 2 * threadIdx.x; i <= ni; i += 2 * blockDim.x) {
         const long long o = ro + i;
-        const double pc = p[o];
-        double un, vn;
+        const bool two = (i + 1 <= ni);                          // the second cell of the pair is an interior cell
+        const double2 pc = *reinterpret_cast<const double2*>(p + o);
+        double2 un, vn;
         if (UPDATE) {
             // u, v are only READ where the update does not reach (last column / last row): the rest
             // of the pass reads F, G, p and writes u, v -- 40 B per cell
-            if (i <= ni - 1) {
-                un = __dsub_rn(F[o], __dmul_rn(m.dt, nsb_div<RECIPD>(__dsub_rn(p[o + 1], pc), m.dx, m.rdx)));
-                u[o] = un;
+            const double2 f = *reinterpret_cast<const double2*>(F + o);
+            const double pe2 = p[o + 2];
+            un.x = (i <= ni - 1) ? __dsub_rn(f.x, __dmul_rn(m.dt, nsb_div<RECIPD>(__dsub_rn(pc.y, pc.x), m.dx, m.rdx))) : u[o];
+            un.y = (i + 1 <= ni - 1) ? __dsub_rn(f.y, __dmul_rn(m.dt, nsb_div<RECIPD>(__dsub_rn(pe2, pc.y), m.dx, m.rdx))) : (two ? u[o + 1] : 0.0);
+            if (i + 1 <= ni - 1) *reinterpret_cast<double2*>(u + o) = un;
+            else if (i <= ni - 1) u[o] = un.x;
+            if (v_row) {
+                const double2 g = *reinterpret_cast<const double2*>(G + o);
+                const double2 pn = *reinterpret_cast<const double2*>(p + o + pitch);
+                vn.x = __dsub_rn(g.x, __dmul_rn(m.dt, nsb_div<RECIPD>(__dsub_rn(pn.x, pc.x), m.dy, m.rdy)));
+                vn.y = __dsub_rn(g.y, __dmul_rn(m.dt, nsb_div<RECIPD>(__dsub_rn(pn.y, pc.y), m.dy, m.rdy)));
+                if (two) *reinterpret_cast<double2*>(v + o) = vn;
+                else v[o] = vn.x;
             } else {
-                un = u[o];
-            }
-            if (j <= ra.v_hi) {                                  // global j <= j_max-1 (main.c:134)
-                vn = __dsub_rn(G[o], __dmul_rn(m.dt, nsb_div<RECIPD>(__dsub_rn(p[o + pitch], pc), m.dy, m.rdy)));
-                v[o] = vn;
-            } else {
-                vn = v[o];
+                vn.x = v[o]; vn.y = two ? v[o + 1] : 0.0;
             }
         } else {
-            un = u[o]; vn = v[o];
+            un.x = u[o]; vn.x = v[o];
+            un.y = two ? u[o + 1] : 0.0; vn.y = two ? v[o + 1] : 0.0;
         }
-        mu = fmax(mu, un);
-        mv = fmax(mv, vn);
-        sp = fma(pc, pc, sp);
+        mu = fmax(mu, un.x); mv = fmax(mv, vn.x); sp = fma(pc.x, pc.x, sp);
+        if (two) { mu = fmax(mu, un.y); mv = fmax(mv, vn.y); sp = fma(pc.y, pc.y, sp); }
     }
-    const int nblk = gridDim.x * gridDim.y;
-    const int bid = blockIdx.y * gridDim.x + blockIdx.x;
+    const int nblk = gridDim.x;
+    const int bid = blockIdx.x;
     double bu = block_max(mu, sh);
     double bv = block_max(mv, sh);
     double bs = block_sum(sp, sh);
@@ -291,7 +302,7 @@ __global__ void __launch_bounds__(256) update_uv_kernel(double* __restrict__ u, 
         // partials combined in a fixed order; the bands are then combined over ALL slabs in an order
         // that depends on the global band count only (slab.cuh)
         __threadfence();
-        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, gx = gridDim.x;
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, gx = 1;
         for (int b = warp; b < ra.n_chunks; b += 8) {
             const int r0 = b * ra.chunk_rows;
             const int rows = min(ra.chunk_rows, nj - r0);
@@ -334,7 +345,7 @@ cudaError_t nsb_launch_red_close(nsb_ctx* c) {
 }
 
 static void uv_grid(const nsb_ctx* c, dim3& g) {
-    g = dim3(min((c->g.ni + 255) / 256, 4), c->g.nj);
+    g = dim3(c->g.nj);                                         // one block per row
 }
 
 static UvRedArgs uv_red_args(nsb_ctx* c) {

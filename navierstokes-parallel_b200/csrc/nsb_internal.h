@@ -217,7 +217,6 @@ SorCoef nsb_make_sor_coef(nsb_ctx* c, long long cells);                  // sor_
 cudaError_t nsb_launch_sor_finish_ghosts(nsb_ctx* c, double* pfinal, const double* pprev);
 cudaError_t nsb_launch_to_xfast(nsb_ctx* c, const double* src_ref, double* dst);   // [i][j] -> grid
 cudaError_t nsb_launch_from_xfast(nsb_ctx* c, const double* src, double* dst_ref); // grid -> [i][j]
-cudaError_t nsb_launch_pack_xfast(nsb_ctx* c, const double* src, double* dst_dense, int to_dense);
 int nsb_sor_resident_supported(const nsb_ctx* c);
 cudaError_t nsb_launch_sor_resident(nsb_ctx* c, int max_it, int check);
 
