@@ -12,7 +12,7 @@ for r in rows:
     tot[r[ki]] += float(r[vi].replace(",", "")) / 1e3
     cnt[r[ki]] += 1
 total = sum(tot.values())
-print(f"{tag}: ncu launch list of `python bench.py --steps 2 --warmup 1 --max-it 20 --no-e2e --no-cpu-baseline` (8192^2, B200)")
+print(f"{tag}: ncu launch list of `python bench.py --steps 2 --warmup 1 --max-it 20 --no-e2e --no-cpu-baseline --no-parity` (8192^2, B200)")
 print("ncu --metrics gpu__time_duration.sum --clock-control none -c 400   (cold-cache, serialised: compare SHARES)")
 print(f"{len(rows)} launches, {total:.1f} us in kernels")
 for k, v in tot.most_common():
