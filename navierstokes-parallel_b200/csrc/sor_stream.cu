@@ -65,9 +65,25 @@ static_assert(SOR_BLK % (2 * SOR_NST) == 0, "SOR_BLK must be a multiple of 2 * S
 // carries one more column group on either side of the 32 the lanes own (one more input column is needed there, see
 // sor_colour): 34 groups = 1088 B.
 #define SOR_PROW_BYTES(K) (SOR_ROW_BYTES + ((K) > 1 ? 64 : 0))
-#define SOR_STAGE_BYTES(K) (2 * SOR_PROW_BYTES(K) + 2 * SOR_ROW_BYTES)
-#define SOR_WARP_SMEM(K) (SOR_NST * SOR_STAGE_BYTES(K))
-#define SOR_SMEM_BYTES(K) (SOR_WARPS * SOR_WARP_SMEM(K) + SOR_WARPS * 2 * SOR_NST * 8)   // rings + FULL/EMPTY mbarriers
+// K > 1 (SOR_RS): the RHS rows are NOT copied into the register window -- a row is used in six consecutive steps, and 7 rows
+// of RHS are 56 registers, the difference between 8 and 10 resident warps per SM.  They stay in a ring of SOR_RS_PAIRS row
+// pairs in shared memory (a pair is loaded with its p pair, under the same FULL barrier, and is dead 7 steps later: with 8
+// pairs in the ring a slot is rewritten 11 steps after its last read) and every phase reads the words it needs.
+// MEASURED AND NOT KEPT AS THE DEFAULT (profiles/r2y_rs_experiment.txt): at 200 registers it is still 8 warps per SM;
+// forced to 168 registers (12 warps, 40 B of spills) the sweep takes 207 us per iteration at 8192^2 against 192 us with the
+// RHS in registers -- the shared-memory loads sit right in front of their use (short_scoreboard 2.3 of 8.5 stall cycles
+// per issue) and the spills add local-memory traffic (long_scoreboard 1.25).  -DSOR_K2_RHS_SMEM=1 builds it.
+#ifndef SOR_K2_RHS_SMEM
+#define SOR_K2_RHS_SMEM 0
+#endif
+#define SOR_RS(K) ((K) > 1 && SOR_K2_RHS_SMEM)
+#define SOR_RS_PAIRS 6                                            // 12 warps x (4.25 KB of p stages + 12 KB of RHS ring) = 195 KB per SM
+#define SOR_KWARPS(K) (SOR_WARPS)                                 // warps per block
+#define SOR_KTHREADS(K) (SOR_KWARPS(K) * 32)
+#define SOR_STAGE_BYTES(K) (2 * SOR_PROW_BYTES(K) + (SOR_RS(K) ? 0 : 2 * SOR_ROW_BYTES))
+#define SOR_RING_BYTES(K) (SOR_NST * SOR_STAGE_BYTES(K))          // the p (+ RHS) stages of one warp
+#define SOR_WARP_SMEM(K) (SOR_RING_BYTES(K) + (SOR_RS(K) ? SOR_RS_PAIRS * 2 * SOR_ROW_BYTES : 0))
+#define SOR_SMEM_BYTES(K) (SOR_KWARPS(K) * SOR_WARP_SMEM(K) + SOR_KWARPS(K) * 2 * SOR_NST * 8)   // rings + FULL/EMPTY mbarriers
 // Temporal blocking (K sub-iterations per pass over HBM).  A row that arrived in step j goes through
 //     red (lag 1), black (lag 2), residual (lag 3)        of sub-iteration 0,
 //     red (lag 4), black (lag 5), residual (lag 6)        of sub-iteration 1, ...
@@ -246,6 +262,10 @@ struct TaskCtx {
     uint32_t copy_bytes_p;    // bytes per p row copy (K > 1: one more group on either side)
     double ex;                // K > 1: the extra input column of the row that arrived in the previous step (lane 0: west, lane 31: east)
     uint32_t smem_base;       // this warp's ring (shared address)
+    uint32_t rs_base;         // SOR_RS: this warp's RHS ring (shared address); rs_lane = generic pointer + 4 * lane doubles
+    const double* rs_lane;
+    int rs_pair;              // SOR_RS: pairs issued so far in this task (slot = rs_pair & 7)
+    int rs_h;                 // SOR_RS: ring slot of the current block's first pair
     long long ld_step;        // 2 * pitch (0 with the developer probe NSB_DEBUG_FIXED_LOADS: every pair re-reads the same two rows)
 };
 
@@ -274,18 +294,35 @@ __device__ __forceinline__ void issue_pair(TaskCtx& t, int st, uint32_t empty_ph
         if (wait_empty) mbar_wait(t.bar_base + (SOR_NST + st) * 8, empty_phase);
         if (t.j_next <= t.j_limit) {
             const uint32_t dst = t.smem_base + st * SOR_STAGE_BYTES(K);
+            const uint32_t rdst = SOR_RS(K) ? t.rs_base + (uint32_t)(t.rs_pair % SOR_RS_PAIRS) * (2u * SOR_ROW_BYTES)
+                                            : dst + 2 * SOR_PROW_BYTES(K);
             mbar_expect_tx(bar, 2u * t.copy_bytes_p + 2u * t.copy_bytes);
             bulk_g2s(dst, t.pin_next, t.copy_bytes_p, bar);
             bulk_g2s(dst + SOR_PROW_BYTES(K), t.pin_next + t.pitch, t.copy_bytes_p, bar);
-            bulk_g2s(dst + 2 * SOR_PROW_BYTES(K), t.rhs_next, t.copy_bytes, bar);
-            bulk_g2s(dst + 2 * SOR_PROW_BYTES(K) + SOR_ROW_BYTES, t.rhs_next + t.pitch, t.copy_bytes, bar);
+            bulk_g2s(rdst, t.rhs_next, t.copy_bytes, bar);
+            bulk_g2s(rdst + SOR_ROW_BYTES, t.rhs_next + t.pitch, t.copy_bytes, bar);
         } else {
             mbar_arrive(bar);
         }
     }
     t.j_next += 2;
+    t.rs_pair += 1;
     t.pin_next += t.ld_step;
     t.rhs_next += t.ld_step;
+}
+
+// SOR_RS: the RHS row of the phase with lag L in step S of a block (row j - L), this lane's 4 columns.  The block's first
+// pair sits in ring slot t.rs_h = (pairs before the block) mod 6 (warp-uniform, set per block); the pair of this phase is d
+// pairs further (d compile-time, -3 .. 3).
+template <int S, int L>
+__device__ __forceinline__ const double* sor_rs_row(const TaskCtx& t) {
+    constexpr int rel = S - L;
+    constexpr int d = (rel >= 0) ? rel / 2 : -((-rel + 1) / 2);     // floor(rel / 2): pair relative to the block's first
+    constexpr int par = rel - 2 * d;                                 // row of the pair
+    int slot = t.rs_h + d;
+    if (d < 0) { if (slot < 0) slot += SOR_RS_PAIRS; }
+    else if (d > 0) { if (slot >= SOR_RS_PAIRS) slot -= SOR_RS_PAIRS; }
+    return t.rs_lane + slot * (2 * SOR_ROW_BYTES / 8) + par * (SOR_ROW_BYTES / 8);
 }
 
 // ---- one colour phase: sub-iteration Q's red (L = 3Q+1) or black (L = 3Q+2) update of row j - L.
@@ -339,8 +376,11 @@ __device__ __forceinline__ void sor_colour(double (&P)[SOR_BLK][4], double (&R)[
     const double w1 = X[c1 - 1];
     const double e1 = (c1 == 3) ? xe : X[(c1 + 1) & 3];
     bool ok0 = true, ok1 = true;
-    const double u0 = sor_cell_q<QM>(X[c0], e0, w0, P[sN][c0], P[sS][c0], R[sX][c0], kf, EX ? ok0 : ok);
-    const double u1 = sor_cell_q<QM>(X[c1], e1, w1, P[sN][c1], P[sS][c1], R[sX][c1], kf, EX ? ok1 : ok);
+    double rh0, rh1;
+    if constexpr (SOR_RS(K)) { const double* rr = sor_rs_row<S, L>(t); rh0 = rr[c0]; rh1 = rr[c1]; }
+    else { rh0 = R[sX][c0]; rh1 = R[sX][c1]; }
+    const double u0 = sor_cell_q<QM>(X[c0], e0, w0, P[sN][c0], P[sS][c0], rh0, kf, EX ? ok0 : ok);
+    const double u1 = sor_cell_q<QM>(X[c1], e1, w1, P[sN][c1], P[sS][c1], rh1, kf, EX ? ok1 : ok);
     if (EX) {
         if (row_in && lg.inner[c0]) { X[c0] = u0; ok = ok && ok0; }
         if (row_in && lg.inner[c1]) { X[c1] = u1; ok = ok && ok1; }
@@ -412,12 +452,21 @@ __device__ __forceinline__ void sor_resid(double (&P)[SOR_BLK][4], double (&R)[S
     const double xe = __shfl_down_sync(FULL, X[0], 1);
     if (r >= t.jc0 && r <= t.jc1) {            // warp-uniform; rows of the chunk are interior rows
         double part = 0.0;
+        double rh[4];
+        if constexpr (SOR_RS(K)) {
+            const double2* rr = reinterpret_cast<const double2*>(sor_rs_row<S, L>(t));
+            const double2 ra = rr[0], rb = rr[1];
+            rh[0] = ra.x; rh[1] = ra.y; rh[2] = rb.x; rh[3] = rb.y;
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; k++) rh[k] = R[sX][k];
+        }
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             const double w = (k == 0) ? xw : X[(k + 3) & 3];
             const double e = (k == 3) ? xe : X[(k + 1) & 3];
             bool okr = true;
-            const double q = sor_residual_q<QM>(X[k], e, w, P[sN][k], P[sS][k], R[sX][k], kf, EX ? okr : ok);
+            const double q = sor_residual_q<QM>(X[k], e, w, P[sN][k], P[sS][k], rh[k], kf, EX ? okr : ok);
             if (!EX || lg.inner[k]) { part = fma(q, q, part); if (EX) ok = ok && okr; }
         }
         if ((MASK || (sor_lanemask_mode(QM, K) == 1 && !EX)) && !lg.li) part = 0.0;        // lanes outside the domain (masked strips)
@@ -460,11 +509,14 @@ __device__ __forceinline__ void sor_step(double (&P)[SOR_BLK][4], double (&R)[SO
 #endif
         }
         const double* prow = t.lds_lane + st * (SOR_STAGE_BYTES(K) / 8) + (S & 1) * (SOR_PROW_BYTES(K) / 8);
-        const double* rrow = t.lds_lane + st * (SOR_STAGE_BYTES(K) / 8) + 2 * (SOR_PROW_BYTES(K) / 8) + (S & 1) * (SOR_ROW_BYTES / 8);
         const double2* q = reinterpret_cast<const double2*>(prow + (K > 1 ? NSB_GROUP : 0));
-        const double2* qr = reinterpret_cast<const double2*>(rrow);
         const double2 a = q[0], b = q[1];
-        const double2 c = qr[0], d = qr[1];
+        double2 c = make_double2(0.0, 0.0), d = make_double2(0.0, 0.0);
+        if constexpr (!SOR_RS(K)) {
+            const double* rrow = t.lds_lane + st * (SOR_STAGE_BYTES(K) / 8) + 2 * (SOR_PROW_BYTES(K) / 8) + (S & 1) * (SOR_ROW_BYTES / 8);
+            const double2* qr = reinterpret_cast<const double2*>(rrow);
+            c = qr[0]; d = qr[1];
+        }
         if (K > 1) {
             // The red update of sub-iteration 0 needs ONE input column beyond the 128 the lanes hold: the west
             // neighbour of lane 0's column 0 in rows where that cell is red, the east neighbour of lane 31's column 3 in
@@ -474,7 +526,7 @@ __device__ __forceinline__ void sor_step(double (&P)[SOR_BLK][4], double (&R)[SO
             ex_new = (S & 1) ? e[NSB_GROUP - 1] : e[NSB_GROUP + 32 * NSB_GROUP];
         }
         P[sE][0] = a.x; P[sE][1] = a.y; P[sE][2] = b.x; P[sE][3] = b.y;
-        R[sE][0] = c.x; R[sE][1] = c.y; R[sE][2] = d.x; R[sE][3] = d.y;
+        if constexpr (!SOR_RS(K)) { R[sE][0] = c.x; R[sE][1] = c.y; R[sE][2] = d.x; R[sE][3] = d.y; }
         if (S & 1) {
             // Both rows of the pair are read: every lane releases the stage on its EMPTY barrier and
             // the elected lane re-arms the stage only after acquiring that phase (32 arrivals).
@@ -484,9 +536,8 @@ __device__ __forceinline__ void sor_step(double (&P)[SOR_BLK][4], double (&R)[SO
             // barrier ADDRESS is made data-dependent on all LDS of the pair (this step's
             // a, b, c, d and the previous step's, now in window slot D): `zero` is a run-time 0 the
             // compiler cannot fold, and the arrive cannot issue before the loads have landed.
-            int dep = (__double2hiint(a.x) ^ __double2hiint(b.x) ^ __double2hiint(c.x)) ^
-                      (__double2hiint(d.x) ^ __double2hiint(P[sD][0]) ^ __double2hiint(P[sD][2])) ^
-                      (__double2hiint(R[sD][0]) ^ __double2hiint(R[sD][2]));
+            int dep = (__double2hiint(a.x) ^ __double2hiint(b.x)) ^ (__double2hiint(P[sD][0]) ^ __double2hiint(P[sD][2]));
+            if constexpr (!SOR_RS(K)) dep ^= (__double2hiint(c.x) ^ __double2hiint(d.x)) ^ (__double2hiint(R[sD][0]) ^ __double2hiint(R[sD][2]));
             if (K > 1) dep ^= __double2hiint(ex_new) ^ __double2hiint(t.ex);
             mbar_arrive(t.bar_base + (SOR_NST + st) * 8 + ((uint32_t)dep & t.zero));
             issue_pair<K>(t, st, ph ^ t.empty_par, true);
@@ -531,6 +582,7 @@ __device__ __forceinline__ void sor_run_task(TaskCtx& t, const SorCoef& kf, cons
     uint32_t use0 = 0u;
     for (int sb = 0; sb < n_steps; sb += SOR_BLK, use0 += SOR_USES_PER_BLK) {
         const int jb = t.jstart + sb;                        // row arriving in the first step of the block
+        if constexpr (SOR_RS(K)) t.rs_h = (sb >> 1) % SOR_RS_PAIRS;
         // rows touched by the block (B = SOR_BLK): residuals jb-3K .. jb+B-4, stores jb-(3K-1) .. jb+B-3K, updates up to jb+B-2, loads jb .. jb+B-1
 #ifdef SOR_NO_LEAN
         const bool clean = false;
@@ -583,6 +635,7 @@ __device__ __forceinline__ void sor_task(TaskCtx& t, const SorCoef& kf, const La
     const double* pin0 = t.pin_next; const double* rhs0 = t.rhs_next; double* pout0 = t.pout_row;
     t.full_par = full_par; t.empty_par = empty_par;
     sor_advance_parities(n_steps, full_par, empty_par);
+    t.rs_pair = 0;
     __syncwarp();
 #pragma unroll
     for (int q = 0; q < SOR_NST; q++) issue_pair<K>(t, q, 0u, false);
@@ -592,6 +645,7 @@ __device__ __forceinline__ void sor_task(TaskCtx& t, const SorCoef& kf, const La
     if (!RECIP) {
         if (!__all_sync(0xffffffffu, ok)) {
             t.pin_next = pin0; t.rhs_next = rhs0; t.pout_row = pout0; t.j_next = t.jstart;
+            t.rs_pair = 0;
             t.full_par = full_par; t.empty_par = empty_par;
             sor_advance_parities(n_steps, full_par, empty_par);
             __syncwarp();
@@ -712,6 +766,7 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
         t.lds_lane = reinterpret_cast<const double*>(ring) + lane * NSB_GROUP;
         t.smem_base = smem_u32(ring);
         t.bar_base = smem_u32(smem_raw + SOR_WARPS * SOR_WARP_SMEM(1) + warp * 2 * SOR_NST * 8);
+        t.rs_base = 0u; t.rs_lane = NULL; t.rs_h = 0; t.rs_pair = 0;
 
         // ---- y-slab: the halo rows this task reads were stored by the neighbour's launch seq-1
         if ((MULTI && (a.world > 1)) && a.it > 0) {    // it == 0: the halo came with the p exchange at the solve entry
@@ -872,14 +927,15 @@ __device__ __forceinline__ void sor_band_sums(const double* part, double* bandva
 }
 
 template <bool RECIP, bool MULTI, int K>
-__global__ void __launch_bounds__(SOR_THREADS, (K == 1 ? SOR_MIN_BLOCKS : SOR_MIN_BLOCKS_K2)) sor_persist_kernel(const SorPersistArgs pa) {
+// registers: 168 (3 blocks of 4 warps) for one iteration per pass; two: 168 with the RHS ring in shared memory, 255 without (2 blocks of 4)
+__global__ void __maxnreg__(K == 1 ? 168 : (SOR_RS(K) ? 168 : 255)) sor_persist_kernel(const SorPersistArgs pa) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const SorStreamArgs& a = pa.s;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned FULLM = 0xffffffffu;
     const unsigned long long total = (unsigned long long)pa.n_pass * (unsigned long long)a.n_tasks;
     unsigned char* ring = smem_raw + warp * SOR_WARP_SMEM(K);
-    const uint32_t bar_base = smem_u32(smem_raw + SOR_WARPS * SOR_WARP_SMEM(K) + warp * 2 * SOR_NST * 8);
+    const uint32_t bar_base = smem_u32(smem_raw + SOR_KWARPS(K) * SOR_WARP_SMEM(K) + warp * 2 * SOR_NST * 8);
     // The mbarriers are initialised once and live across the tasks of this warp.  Per task and stage
     // the FULL barrier completes (pairs per stage + 1) phases (the last re-arm is never waited for, it
     // is a plain arrive), the EMPTY barrier (pairs per stage): the parities a task starts with follow.
@@ -955,6 +1011,9 @@ __global__ void __launch_bounds__(SOR_THREADS, (K == 1 ? SOR_MIN_BLOCKS : SOR_MI
         t.lds_lane = reinterpret_cast<const double*>(ring) + lane * NSB_GROUP;
         t.smem_base = smem_u32(ring);
         t.bar_base = bar_base;
+        t.rs_base = smem_u32(ring + SOR_RING_BYTES(K));
+        t.rs_lane = reinterpret_cast<const double*>(ring + SOR_RING_BYTES(K)) + lane * NSB_GROUP;
+        t.rs_h = 0; t.rs_pair = 0;
 
         // ---- y-slab: rows of the previous pass pushed by the neighbouring ranks (their boundary
         //      tasks of pass ps-1, strips s-1 .. s+1); a.seq = halo epoch of "before pass 0"
@@ -1162,14 +1221,17 @@ void nsb_sor_plan(nsb_ctx* c) {
         cudaFuncSetAttribute((const void*)sor_stream_fn(v & 1, v & 2), cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES(1));
         cudaFuncSetAttribute((const void*)sor_persist_fn(v & 1, v & 2, 1), cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES(1));
         cudaFuncSetAttribute((const void*)sor_persist_fn(v & 1, v & 2, 2), cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES(2));
+        // two blocks of the RHS-ring variant need 2 x 102 KB: ask for the largest shared-memory carve-out (the default
+        // carve-out fitted ONE block: 5 warps per SM, profiles/r2w)
+        cudaFuncSetAttribute((const void*)sor_persist_fn(v & 1, v & 2, 2), cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     }
     c->n_strips = (ni + NSB_STRIP_COLS - 1) / NSB_STRIP_COLS;
     long long slots[3] = {0, 0, 0};
     for (int k = 1; k <= 2; k++) {
         int bps = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (const void*)sor_persist_fn(c->use_recip, c->world > 1, k), SOR_THREADS, SOR_SMEM_BYTES(k));
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (const void*)sor_persist_fn(c->use_recip, c->world > 1, k), SOR_KTHREADS(k), SOR_SMEM_BYTES(k));
         if (bps < 1) bps = 1;
-        slots[k] = (long long)c->sm_count * bps * SOR_WARPS;
+        slots[k] = (long long)c->sm_count * bps * SOR_KWARPS(k);
     }
     int want = c->O.sor_pass_k >= 1 && c->O.sor_pass_k <= NSB_SOR_KMAX ? c->O.sor_pass_k : 0;      // 0 = by the model
     {
@@ -1309,16 +1371,17 @@ cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int k, int n_pass, int it0, int c
     int bps = 0;
     // (developer probe NSB_DEBUG_FORCE_MULTI: the multi-slab instantiation on a single slab -- what the extra code costs without any exchange)
     const SorPersistFn kern = sor_persist_fn(c->use_recip, c->world > 1 || getenv("NSB_DEBUG_FORCE_MULTI") != NULL, k);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (const void*)kern, SOR_THREADS, SOR_SMEM_BYTES(k));
+    const int kw = SOR_KWARPS(k);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (const void*)kern, SOR_KTHREADS(k), SOR_SMEM_BYTES(k));
     if (bps < 1) bps = 1;
-    const long long want = ((long long)n_pass * a.n_tasks + SOR_WARPS - 1) / SOR_WARPS;
+    const long long want = ((long long)n_pass * a.n_tasks + kw - 1) / kw;
     long long blocks = (long long)c->sm_count * bps;
     if (blocks > want) blocks = want;
     // at most two passes are in flight at any time: more warps than that would only poll flags
-    const long long useful = (2LL * a.n_tasks + SOR_WARPS - 1) / SOR_WARPS + 1;
+    const long long useful = (2LL * a.n_tasks + kw - 1) / kw + 1;
     if (blocks > useful) blocks = useful;
     cudaError_t e = cudaMemsetAsync(c->d_claim, 0, 8 * sizeof(unsigned long long), c->stream);
     if (e != cudaSuccess) return e;
-    kern<<<(int)blocks, SOR_THREADS, SOR_SMEM_BYTES(k), c->stream>>>(pa);
+    kern<<<(int)blocks, SOR_KTHREADS(k), SOR_SMEM_BYTES(k), c->stream>>>(pa);
     return NSB_LAUNCHED(c, 1);
 }
