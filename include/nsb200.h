@@ -241,6 +241,21 @@ int nsb_timestep(const nsb_params* params, double t, double** u, double** v, dou
 /* release the cached context the host-grid API keeps between calls */
 void nsb_host_api_reset(void);
 
+/* ---------------------------------------------------------------- C. allocation-free entry point
+ * No counterpart in the reference; added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * max_mat (io.h:42 semantics: the scan starts from m[0][0] and takes strictly larger values of rows 1..i_max, columns
+ * 1..j_max) of a grid that is ALREADY on the current device: row i starts at d_m + i * row_stride doubles
+ * (row_stride >= j_max + 1; the reference's device grids have row_stride = j_max + 2, main.cu:103-120).  The result is
+ * written to the device double *d_max, asynchronously on `stream` (a cudaStream_t; NULL = the default stream).
+ * Allocates nothing: the per-row partial maxima live in a static device array of 128.25 KiB that every GPU loading
+ * the library holds until exit.  Limits: i_max <= 16384 and j_max <= 16384, beyond that NSB_ERR_ARG with the text in
+ * nsb_last_error(NULL).  All calls on one device share that array: calls that overlap on the GPU (two streams) race;
+ * calls ordered on one stream do not.  The first call on a device looks the array's address up (make it outside
+ * stream capture). */
+int nsb_max_mat_noalloc(const double* d_m, long long row_stride, int i_max, int j_max, double* d_max, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

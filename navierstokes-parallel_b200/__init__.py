@@ -119,6 +119,7 @@ ABI = {
     "nsb_max_mat": (C.c_double, [C.c_int, C.c_int, dbl_pp]),
     "nsb_timestep": (C.c_int, [C.POINTER(Params), C.c_double] + [dbl_pp] * 6 + [C.POINTER(StepInfo)]),
     "nsb_host_api_reset": (None, []),
+    "nsb_max_mat_noalloc": (C.c_int, [C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     # y-slab decomposition
     "nsb_slab_partition": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, int_p, int_p, int_p, int_p]),
     "nsb_create_slab": (C.c_int, [C.POINTER(Params), C.POINTER(Options), C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
