@@ -83,7 +83,8 @@ static_assert(SOR_BLK % (2 * SOR_NST) == 0, "SOR_BLK must be a multiple of 2 * S
 #define SOR_STAGE_BYTES(K) (2 * SOR_PROW_BYTES(K) + (SOR_RS(K) ? 0 : 2 * SOR_ROW_BYTES))
 #define SOR_RING_BYTES(K) (SOR_NST * SOR_STAGE_BYTES(K))          // the p (+ RHS) stages of one warp
 #define SOR_WARP_SMEM(K) (SOR_RING_BYTES(K) + (SOR_RS(K) ? SOR_RS_PAIRS * 2 * SOR_ROW_BYTES : 0))
-#define SOR_SMEM_BYTES(K) (SOR_KWARPS(K) * SOR_WARP_SMEM(K) + SOR_KWARPS(K) * 2 * SOR_NST * 8)   // rings + FULL/EMPTY mbarriers
+#define SOR_BAR_BYTES (2 * SOR_NST * 8 + 16)                      // per warp: FULL/EMPTY mbarriers + the two push distances
+#define SOR_SMEM_BYTES(K) (SOR_KWARPS(K) * SOR_WARP_SMEM(K) + SOR_KWARPS(K) * SOR_BAR_BYTES)   // rings + barrier blocks
 // Temporal blocking (K sub-iterations per pass over HBM).  A row that arrived in step j goes through
 //     red (lag 1), black (lag 2), residual (lag 3)        of sub-iteration 0,
 //     red (lag 4), black (lag 5), residual (lag 6)        of sub-iteration 1, ...
@@ -148,6 +149,14 @@ struct SorStreamArgs {
 
 // ---------------------------------------------------------------- mbarrier / bulk-copy PTX
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ long long lds_s64(uint32_t addr) {
+    long long v;
+    asm volatile("ld.shared.s64 %0, [%1];" : "=l"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_s64(uint32_t addr, long long v) {
+    asm volatile("st.shared.s64 [%0], %1;" ::"r"(addr), "l"(v) : "memory");
+}
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
@@ -242,10 +251,17 @@ __device__ __forceinline__ void refresh_ghost_columns(double (&X)[4], const Lane
 struct TaskCtx {
     int jstart, jc0, jc1;
     int nj;
-    bool wall_bottom, wall_top;
-    bool push_down, push_up;  // this task owns rows of the neighbour's halo
-    double* down_col; double* up_col;   // neighbour's pout, this lane's column group, row 0 of its storage
-    int down_nj;
+    // Slab geometry of the task in ONE register (bit 0 / 1: the slab's bottom / top is a wall of the domain; bit 2 / 3:
+    // this task owns rows of the lower / upper neighbour's halo).  Where the pushed rows go is not kept in registers at
+    // all: the byte distance from this slab's output row to the same row in the neighbour's halo sits in two shared-memory
+    // words of the warp (sor_task_buffers), read only on the <= 5 rows per boundary task that are pushed.  (r2: two
+    // pointers, a row count and four flags were live across the hot body of the multi-slab instantiation.)
+    uint32_t mf;
+    uint32_t push_slot;       // shared address of {down, up} byte distances
+    __device__ __forceinline__ bool wall_bottom() const { return (mf & 1u) != 0u; }
+    __device__ __forceinline__ bool wall_top() const { return (mf & 2u) != 0u; }
+    __device__ __forceinline__ bool push_down() const { return (mf & 4u) != 0u; }
+    __device__ __forceinline__ bool push_up() const { return (mf & 8u) != 0u; }
     long long pitch;
     double* pout_row;         // &pout[row of the black update of the current step][this lane's group]
     const double* lds_lane;   // generic pointer: this warp's ring + 4 * lane doubles
@@ -349,17 +365,17 @@ __device__ __forceinline__ void sor_colour(double (&P)[SOR_BLK][4], double (&R)[
     constexpr int margin = 1 + 2 * (K - 1 - Q);
     const unsigned FULL = 0xffffffffu;
     const int r = j - L;
-    const bool row_in = !EY || ((r >= (t.wall_bottom ? 1 : -margin)) && (r <= (t.wall_top ? t.nj : t.nj + 1 + margin)));
+    const bool row_in = !EY || ((r >= (t.wall_bottom() ? 1 : -margin)) && (r <= (t.wall_top() ? t.nj : t.nj + 1 + margin)));
     double (&X)[4] = P[sX];
     constexpr int LM = sor_lanemask_mode(QM, K);
     const bool mask = MASK || (LM == 1 && !EX && lg.masked);
     if (EX || mask) refresh_ghost_columns(X, lg);                       // main.cu:686 / 694
     if (EY) {
-        if (r == 1 && t.wall_bottom) {
+        if (r == 1 && t.wall_bottom()) {
 #pragma unroll
             for (int k = 0; k < 4; k++) P[sS][k] = X[k];                // p[i][0] = p[i][1]
         }
-        if (r == t.nj && t.wall_top) {
+        if (r == t.nj && t.wall_top()) {
 #pragma unroll
             for (int k = 0; k < 4; k++) P[sN][k] = X[k];                // p[i][j_max+1] = p[i][j_max]
         }
@@ -410,25 +426,25 @@ __device__ __forceinline__ void sor_colour(double (&P)[SOR_BLK][4], double (&R)[
             if (EY) {
                 // ghost rows j = 0 / j_max+1 as the same refresh left them (copies of row 1 / j_max taken
                 // before the black update, held in the window slots south / north of the row)
-                if (r == 1 && t.wall_bottom) {
+                if (r == 1 && t.wall_bottom()) {
                     double2* h = reinterpret_cast<double2*>(t.pout_row - t.pitch);
                     h[0] = make_double2(P[sS][0], P[sS][1]);
                     h[1] = make_double2(P[sS][2], P[sS][3]);
                 }
-                if (r == t.nj && t.wall_top) {
+                if (r == t.nj && t.wall_top()) {
                     double2* h = reinterpret_cast<double2*>(t.pout_row + t.pitch);
                     h[0] = make_double2(P[sN][0], P[sN][1]);
                     h[1] = make_double2(P[sN][2], P[sN][3]);
                 }
                 // y-slab halo: the HALO rows next to a slab boundary also go straight into the
                 // neighbour's halo rows over NVLink (peer store), SURVEY 8e
-                if (t.push_down && r <= HALO) {
-                    double2* h = reinterpret_cast<double2*>(t.down_col + (long long)(t.down_nj + r + NSB_ROW0) * t.pitch);
+                if (t.push_down() && r <= HALO) {
+                    double2* h = reinterpret_cast<double2*>(reinterpret_cast<char*>(t.pout_row) + lds_s64(t.push_slot));
                     h[0] = make_double2(X[0], X[1]);
                     h[1] = make_double2(X[2], X[3]);
                 }
-                if (t.push_up && r >= t.nj - HALO + 1) {
-                    double2* h = reinterpret_cast<double2*>(t.up_col + (long long)(r - t.nj + NSB_ROW0) * t.pitch);
+                if (t.push_up() && r >= t.nj - HALO + 1) {
+                    double2* h = reinterpret_cast<double2*>(reinterpret_cast<char*>(t.pout_row) + lds_s64(t.push_slot + 8u));
                     h[0] = make_double2(X[0], X[1]);
                     h[1] = make_double2(X[2], X[3]);
                 }
@@ -593,8 +609,8 @@ __device__ __forceinline__ void sor_run_task(TaskCtx& t, const SorCoef& kf, cons
         // (r1: a separate chunk-edge body made the kernel larger and slower; the gates cost ~3 % of the plain body's
         // instructions and keep the edge blocks of short chunks out of the 2.5 x larger wall body.)
         constexpr int LS = SorK<K>::LAG_STORE, HALO = SorK<K>::HALO;
-        const bool clean = (!t.wall_bottom || jb - LS >= 2) && (!t.wall_top || jb + SOR_BLK - 2 <= t.nj - 1) &&
-                           !(t.push_down && jb - LS <= HALO) && !(t.push_up && jb + SOR_BLK - 1 - LS >= t.nj - HALO + 1);
+        const bool clean = (!t.wall_bottom() || jb - LS >= 2) && (!t.wall_top() || jb + SOR_BLK - 2 <= t.nj - 1) &&
+                           !(t.push_down() && jb - LS <= HALO) && !(t.push_up() && jb + SOR_BLK - 1 - LS >= t.nj - HALO + 1);
 #endif
         // (a fourth variant <EX, !EY> for the interior rows of the two edge strips was measured: the larger
         //  kernel body costs the LEAN path 10 % -- 5.27 against 5.86 TB/s at 8192^2 -- and was dropped)
@@ -700,16 +716,17 @@ __device__ __forceinline__ void sor_task_geometry(TaskCtx& t, LaneGeom& lg, bool
     t.jc1 = min(t.jc0 + a.chunk_rows - 1, a.nj);
     t.jstart = t.jc0 - HALO;                             // even, because chunk_rows is even and HALO is odd
     t.nj = a.nj;
-    t.wall_bottom = !(MULTI && (a.wall_bottom == 0)); t.wall_top = !(MULTI && (a.wall_top == 0));
-    t.push_down = (MULTI && (!t.wall_bottom && t.jc0 <= HALO));
-    t.push_up = (MULTI && (!t.wall_top && t.jc1 >= a.nj - HALO + 1));
+    {
+        const bool wb = !(MULTI && (a.wall_bottom == 0)), wt = !(MULTI && (a.wall_top == 0));
+        const bool pd = (MULTI && (!wb && t.jc0 <= HALO)), pu = (MULTI && (!wt && t.jc1 >= a.nj - HALO + 1));
+        t.mf = (wb ? 1u : 0u) | (wt ? 2u : 0u) | (pd ? 4u : 0u) | (pu ? 8u : 0u);
+    }
     t.pitch = a.pitch;
     t.ld_step = a.dbg_fixed_loads ? 0 : 2 * a.pitch;
     t.lane = lane;
     t.zero = a.zero;
     t.j_next = t.jstart;
     t.j_limit = min(t.jc1 + HALO, a.nj + HALO);
-    t.down_nj = a.down_nj;
     const int groups_here = min(32, a.n_groups - g0);
     t.copy_bytes = (uint32_t)groups_here * 32u;
     t.copy_bytes_p = K > 1 ? (uint32_t)min(34, a.n_groups - g0 + 1) * 32u : t.copy_bytes;   // from group g0 - 1
@@ -717,16 +734,28 @@ __device__ __forceinline__ void sor_task_geometry(TaskCtx& t, LaneGeom& lg, bool
 }
 
 // Buffers of a task: first rows to fetch, first row to store, the neighbours' halo rows.
+// Row r of this slab's output is at pout + (r + ROW0) * pitch + column; the same row in the lower neighbour's upper halo
+// at down_pout + (down_nj + r + ROW0) * pitch + column, in the upper neighbour's lower halo at
+// up_pout + (r - nj + ROW0) * pitch + column: two byte distances per task, kept in the warp's shared-memory slot.
 template <int K>
 __device__ __forceinline__ void sor_task_buffers(TaskCtx& t, const double* pin, double* pout, const double* rhs,
-                                                 double* down_pout, double* up_pout, int strip, int lane) {
+                                                 double* down_pout, double* up_pout, int down_nj, uint32_t push_slot,
+                                                 int strip, int lane) {
+    t.push_slot = push_slot;
+    if ((t.mf & 12u) && lane == 0) {
+        const long long dd = (long long)(reinterpret_cast<const char*>(down_pout) - reinterpret_cast<const char*>(pout)) +
+                             (long long)down_nj * t.pitch * 8;
+        const long long du = (long long)(reinterpret_cast<const char*>(up_pout) - reinterpret_cast<const char*>(pout)) -
+                             (long long)t.nj * t.pitch * 8;
+        sts_s64(push_slot, dd);
+        sts_s64(push_slot + 8u, du);
+    }
+    __syncwarp();
     const long long coff = (long long)strip * NSB_STRIP_GROUPS * NSB_GROUP;    // first column of the strip
     const long long row_first = (long long)(t.jstart + NSB_ROW0) * t.pitch;
     t.pin_next = pin + row_first + coff - (K > 1 ? NSB_GROUP : 0);     // K > 1: the copy starts one group to the left
     t.rhs_next = rhs + row_first + coff;
     t.pout_row = pout + row_first - SorK<K>::LAG_STORE * t.pitch + coff + (long long)lane * NSB_GROUP;
-    t.down_col = down_pout + coff + (long long)lane * NSB_GROUP;
-    t.up_col = up_pout + coff + (long long)lane * NSB_GROUP;
 }
 
 #ifdef SOR_MAXNREG
@@ -761,17 +790,17 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
         bool edge_strip;
         sor_task_geometry<RECIP, MULTI, 1>(t, lg, edge_strip, a, strip, chunk, lane);
         t.full_par = 0u; t.empty_par = 0u;
-        sor_task_buffers<1>(t, a.pin, a.pout, a.rhs, a.down_pout, a.up_pout, strip, lane);
+        t.bar_base = smem_u32(smem_raw + SOR_WARPS * SOR_WARP_SMEM(1) + warp * SOR_BAR_BYTES);
+        sor_task_buffers<1>(t, a.pin, a.pout, a.rhs, a.down_pout, a.up_pout, a.down_nj, t.bar_base + 2 * SOR_NST * 8, strip, lane);
         unsigned char* ring = smem_raw + warp * SOR_WARP_SMEM(1);
         t.lds_lane = reinterpret_cast<const double*>(ring) + lane * NSB_GROUP;
         t.smem_base = smem_u32(ring);
-        t.bar_base = smem_u32(smem_raw + SOR_WARPS * SOR_WARP_SMEM(1) + warp * 2 * SOR_NST * 8);
         t.rs_base = 0u; t.rs_lane = NULL; t.rs_h = 0; t.rs_pair = 0;
 
         // ---- y-slab: the halo rows this task reads were stored by the neighbour's launch seq-1
         if ((MULTI && (a.world > 1)) && a.it > 0) {    // it == 0: the halo came with the p exchange at the solve entry
-            const bool need_down = !t.wall_bottom && t.jc0 - 3 <= 0;
-            const bool need_up = !t.wall_top && t.jc1 + 3 >= a.nj + 1;
+            const bool need_down = !t.wall_bottom() && t.jc0 - 3 <= 0;
+            const bool need_up = !t.wall_top() && t.jc1 + 3 >= a.nj + 1;
             if (lane < 3) {
                 const int sidx = strip - 1 + lane;           // the columns read belong to strips s-1, s, s+1
                 if (sidx >= 0 && sidx < a.n_strips) {
@@ -798,12 +827,12 @@ __global__ void SOR_KERNEL_ATTR sor_stream_kernel(const SorStreamArgs a) {
         const double acc = warp_sum(accs[0]);
         if (lane == 0) a.partials[chunk * a.n_strips + strip] = acc;
 
-        if (t.push_down || t.push_up) {                      // halo rows are out: tell the neighbour(s)
+        if (t.push_down() || t.push_up()) {                      // halo rows are out: tell the neighbour(s)
             __threadfence_system();
             __syncwarp();
             if (lane == 0) {
-                if (t.push_down) st_release_sys(a.down_flag + strip, a.seq + 1ull);
-                if (t.push_up) st_release_sys(a.up_flag + strip, a.seq + 1ull);
+                if (t.push_down()) st_release_sys(a.down_flag + strip, a.seq + 1ull);
+                if (t.push_up()) st_release_sys(a.up_flag + strip, a.seq + 1ull);
             }
         }
     }
@@ -935,7 +964,7 @@ __global__ void __maxnreg__(K == 1 ? 168 : (SOR_RS(K) ? 168 : 255)) sor_persist_
     const unsigned FULLM = 0xffffffffu;
     const unsigned long long total = (unsigned long long)pa.n_pass * (unsigned long long)a.n_tasks;
     unsigned char* ring = smem_raw + warp * SOR_WARP_SMEM(K);
-    const uint32_t bar_base = smem_u32(smem_raw + SOR_KWARPS(K) * SOR_WARP_SMEM(K) + warp * 2 * SOR_NST * 8);
+    const uint32_t bar_base = smem_u32(smem_raw + SOR_KWARPS(K) * SOR_WARP_SMEM(K) + warp * SOR_BAR_BYTES);
     // The mbarriers are initialised once and live across the tasks of this warp.  Per task and stage
     // the FULL barrier completes (pairs per stage + 1) phases (the last re-arm is never waited for, it
     // is a plain arrive), the EMPTY barrier (pairs per stage): the parities a task starts with follow.
@@ -1007,7 +1036,7 @@ __global__ void __maxnreg__(K == 1 ? 168 : (SOR_RS(K) ? 168 : 255)) sor_persist_
         TaskCtx t;
         bool edge_strip;
         sor_task_geometry<RECIP, MULTI, K>(t, lg, edge_strip, a, strip, chunk, lane);
-        sor_task_buffers<K>(t, pa.own_p[bi], pa.own_p[bo], a.rhs, pa.down_p[bo], pa.up_p[bo], strip, lane);
+        sor_task_buffers<K>(t, pa.own_p[bi], pa.own_p[bo], a.rhs, pa.down_p[bo], pa.up_p[bo], a.down_nj, bar_base + 2 * SOR_NST * 8, strip, lane);
         t.lds_lane = reinterpret_cast<const double*>(ring) + lane * NSB_GROUP;
         t.smem_base = smem_u32(ring);
         t.bar_base = bar_base;
@@ -1018,8 +1047,8 @@ __global__ void __maxnreg__(K == 1 ? 168 : (SOR_RS(K) ? 168 : 255)) sor_persist_
         // ---- y-slab: rows of the previous pass pushed by the neighbouring ranks (their boundary
         //      tasks of pass ps-1, strips s-1 .. s+1); a.seq = halo epoch of "before pass 0"
         if ((MULTI && (a.world > 1)) && (ps > 0 || pa.wait_first)) {
-            const bool need_down = !t.wall_bottom && t.jc0 - SorK<K>::HALO <= 0;
-            const bool need_up = !t.wall_top && t.jc1 + SorK<K>::HALO >= a.nj + 1;
+            const bool need_down = !t.wall_bottom() && t.jc0 - SorK<K>::HALO <= 0;
+            const bool need_up = !t.wall_top() && t.jc1 + SorK<K>::HALO >= a.nj + 1;
             int ok2 = 1;
             if (lane < 3) {
                 const int sidx = strip - 1 + lane;
@@ -1046,12 +1075,12 @@ __global__ void __maxnreg__(K == 1 ? 168 : (SOR_RS(K) ? 168 : 255)) sor_persist_
         __threadfence();
         __syncwarp();
         unsigned long long tk = 0;
-        if (t.push_down || t.push_up) {                      // halo rows are out: tell the neighbouring rank(s)
+        if (t.push_down() || t.push_up()) {                      // halo rows are out: tell the neighbouring rank(s)
             __threadfence_system();
             __syncwarp();
             if (lane == 0) {
-                if (t.push_down) st_release_sys(a.down_flag + strip, a.seq + (unsigned long long)ps + 1ull);
-                if (t.push_up) st_release_sys(a.up_flag + strip, a.seq + (unsigned long long)ps + 1ull);
+                if (t.push_down()) st_release_sys(a.down_flag + strip, a.seq + (unsigned long long)ps + 1ull);
+                if (t.push_up()) st_release_sys(a.up_flag + strip, a.seq + (unsigned long long)ps + 1ull);
             }
         }
         if (lane == 0) {
