@@ -120,45 +120,109 @@ __device__ __forceinline__ double donor_cross(double t1a, double t1b, double t2a
     return __dadd_rn(__dmul_rn(inv_h, __dsub_rn(fa, fb)), __dmul_rn(g_h, __dsub_rn(da, db)));
 }
 
-template <bool RECIP>
-__device__ __forceinline__ double f_cell(const double* __restrict__ U, const double* __restrict__ V,
-                                         long long o, long long pitch, const MomCoef& m) {
-    const double uc = U[o], ue = U[o + 1], uw = U[o - 1], un = U[o + pitch], us = U[o - pitch];
-    const double vc = V[o], ve = V[o + 1], vs = V[o - pitch], vse = V[o - pitch + 1];
-    double visc = __dmul_rn(m.inv_re, lap<RECIP>(uc, ue, uw, un, us, m));
-    double conv_x = donor_self(uc, ue, uw, m.inv_dx, m.g_dx);                       // du2_dx
-    double conv_y = donor_cross(vc, ve, vs, vse, uc, un, us, m.inv_dy, m.g_dy);     // duv_dy
-    double rhs = __dadd_rn(__dsub_rn(__dsub_rn(visc, conv_x), conv_y), m.g_x);
-    return __dadd_rn(uc, __dmul_rn(m.dt, rhs));                                     // integration.c:78-82
+// ---- F and G of one cell from the 3 x 3 neighbourhoods of u and v (index 0 / 1 / 2 = column i-1 / i / i+1; s, c, n =
+// row j-1 / j / j+1), with the y-face terms of the two donor-cell fluxes that run along y carried from row to row.
+//
+// The flux through the face between rows j and j+1 enters row j as its far face (a, fa, da below) and row j+1 as its near
+// face (b, fb, db in donor_self / donor_cross): the same operands in the same operations, additions commuted at most --
+// the same bits.  A thread that marches up a column therefore computes each y-face once: 90 instead of 104 FP64
+// operations per cell (integration.c:17-37 evaluates both faces for every cell), and 6 instead of 18 loads.
+struct FgFaces {
+    double f_fa, f_da;       // duv_dy (F):  (a * 0.5) * (u_j + u_j+1),  (|a| * 0.5) * (u_j - u_j+1),  a = 0.5 (v_i + v_i+1) on row j
+    double g_aa, g_da;       // dv2_dy (G):  a * a,                      (|a| * 0.5) * (v_j - v_j+1),  a = 0.5 (v_j + v_j+1)
+};
+
+// faces between the rows `lo` (j) and `hi` (j+1)
+__device__ __forceinline__ FgFaces fg_faces(const double (&u_lo)[3], const double (&u_hi)[3], const double (&v_lo)[3],
+                                            const double (&v_hi)[3]) {
+    FgFaces f;
+    const double a = __dmul_rn(0.5, __dadd_rn(v_lo[1], v_lo[2]));
+    f.f_fa = __dmul_rn(__dmul_rn(a, 0.5), __dadd_rn(u_lo[1], u_hi[1]));
+    f.f_da = __dmul_rn(__dmul_rn(fabs(a), 0.5), __dsub_rn(u_lo[1], u_hi[1]));
+    const double g = __dmul_rn(0.5, __dadd_rn(v_lo[1], v_hi[1]));
+    f.g_aa = __dmul_rn(g, g);
+    f.g_da = __dmul_rn(__dmul_rn(fabs(g), 0.5), __dsub_rn(v_lo[1], v_hi[1]));
+    return f;
 }
 
+// near = faces below row j (from the previous step), returns F and G of (i, j) and leaves the faces above row j in `near`
 template <bool RECIP>
-__device__ __forceinline__ double g_cell(const double* __restrict__ U, const double* __restrict__ V,
-                                         long long o, long long pitch, const MomCoef& m) {
-    const double vc = V[o], ve = V[o + 1], vw = V[o - 1], vn = V[o + pitch], vs = V[o - pitch];
-    const double uc = U[o], un = U[o + pitch], uw = U[o - 1], uwn = U[o - 1 + pitch];
-    double visc = __dmul_rn(m.inv_re, lap<RECIP>(vc, ve, vw, vn, vs, m));
-    double conv_x = donor_cross(uc, un, uw, uwn, vc, ve, vw, m.inv_dx, m.g_dx);     // duv_dx
-    double conv_y = donor_self(vc, vn, vs, m.inv_dy, m.g_dy);                       // dv2_dy
-    double rhs = __dadd_rn(__dsub_rn(__dsub_rn(visc, conv_x), conv_y), m.g_y);
-    return __dadd_rn(vc, __dmul_rn(m.dt, rhs));                                     // integration.c:86-90
+__device__ __forceinline__ void fg_cell(const double (&us)[3], const double (&uc)[3], const double (&un)[3],
+                                        const double (&vs)[3], const double (&vc)[3], const double (&vn)[3],
+                                        FgFaces& near, const MomCoef& m, double& Fo, double& Go) {
+    const FgFaces far = fg_faces(uc, un, vc, vn);
+    {   // integration.c:73-82
+        const double visc = __dmul_rn(m.inv_re, lap<RECIP>(uc[1], uc[2], uc[0], un[1], us[1], m));
+        const double conv_x = donor_self(uc[1], uc[2], uc[0], m.inv_dx, m.g_dx);                    // du2_dx
+        const double conv_y = __dadd_rn(__dmul_rn(m.inv_dy, __dsub_rn(far.f_fa, near.f_fa)),        // duv_dy
+                                        __dmul_rn(m.g_dy, __dsub_rn(far.f_da, near.f_da)));
+        const double rhs = __dadd_rn(__dsub_rn(__dsub_rn(visc, conv_x), conv_y), m.g_x);
+        Fo = __dadd_rn(uc[1], __dmul_rn(m.dt, rhs));
+    }
+    {   // integration.c:84-90
+        const double visc = __dmul_rn(m.inv_re, lap<RECIP>(vc[1], vc[2], vc[0], vn[1], vs[1], m));
+        const double conv_x = donor_cross(uc[1], un[1], uc[0], un[0], vc[1], vc[2], vc[0], m.inv_dx, m.g_dx);   // duv_dx
+        const double conv_y = __dadd_rn(__dmul_rn(m.inv_dy, __dsub_rn(far.g_aa, near.g_aa)),        // dv2_dy
+                                        __dmul_rn(m.g_dy, __dsub_rn(far.g_da, near.g_da)));
+        const double rhs = __dadd_rn(__dsub_rn(__dsub_rn(visc, conv_x), conv_y), m.g_y);
+        Go = __dadd_rn(vc[1], __dmul_rn(m.dt, rhs));
+    }
+    near = far;
 }
 
+#ifndef FG_BX
+#define FG_BX 128           // columns per block, one per thread
+#endif
+#ifndef FG_ROWS
+#define FG_ROWS 3           // rows marched by a thread (a multiple of 3: the three-row window rotates by renaming)
+#endif
+
+__device__ __forceinline__ void fg_load3(double (&x)[3], const double* __restrict__ p) {
+    x[0] = p[-1]; x[1] = p[0]; x[2] = p[1];
+}
+
+// One thread per column i, marching FG_ROWS rows upwards (r1/r2: one thread per cell, 18 loads and both faces of every
+// flux per cell -- 586 us at 8192^2, FP64 pipe at 64 %, profiles/r2u_ncu_summary.txt).  Measured at 8192^2
+// (profiles/r3_fg_variants.txt, tools/mom_probe.py): 24 rows 463 us, 12 rows 443, 6 rows 427-431, 3 rows 408-425; 256
+// columns per block +60 us; more registers per thread are slower at every height (56 -> 72 by a register cap: +40 us;
+// 78 with the next row's loads issued a step ahead: +45 us) -- the kernel wants resident warps, not longer marches:
+// with 3 rows it still shares 2 of 3 y-faces (94 operations per cell) and loads 10 values per cell.
 template <bool RECIP>
-__global__ void __launch_bounds__(MB_X* MB_Y) fg_kernel(const double* __restrict__ u, const double* __restrict__ v,
-                                                         double* __restrict__ F, double* __restrict__ G,
-                                                         long long pitch, int ni, int nj, int g_hi, MomCoef m) {
-    const int i = blockIdx.x * MB_X + threadIdx.x + 1;
-    const int j = blockIdx.y * MB_Y + threadIdx.y + 1;
-    if (i > ni || j > nj) return;
-    const long long o = (long long)(j + NSB_ROW0) * pitch + NSB_COL0 + i;
-    if (i <= ni - 1) F[o] = f_cell<RECIP>(u, v, o, pitch, m);
-    if (j <= g_hi) G[o] = g_cell<RECIP>(u, v, o, pitch, m);       // global j <= j_max-1 (integration.c:84)
+__global__ void __launch_bounds__(FG_BX) fg_kernel(const double* __restrict__ u, const double* __restrict__ v,
+                                                    double* __restrict__ F, double* __restrict__ G, long long pitch,
+                                                    int ni, int nj, int g_hi, MomCoef m) {
+    const int i = blockIdx.x * FG_BX + threadIdx.x + 1;
+    const int j0 = blockIdx.y * FG_ROWS + 1;
+    if (i > ni) return;
+    const int jend = min(j0 + FG_ROWS - 1, nj);
+    long long o = (long long)(j0 + NSB_ROW0) * pitch + NSB_COL0 + i;            // (i, j0)
+    double ua[3], ub[3], uc[3], va[3], vb[3], vc[3];
+    fg_load3(ua, u + o - pitch); fg_load3(va, v + o - pitch);
+    fg_load3(ub, u + o); fg_load3(vb, v + o);
+    fg_load3(uc, u + o + pitch); fg_load3(vc, v + o + pitch);
+    FgFaces fc = fg_faces(ua, ub, va, vb);
+    const bool f_col = (i <= ni - 1);                                           // integration.c:76
+#define FG_STEP(US, UC, UN, VS, VC, VN, J)                                                          \
+    {                                                                                               \
+        double Fo, Go;                                                                              \
+        fg_cell<RECIP>(US, UC, UN, VS, VC, VN, fc, m, Fo, Go);                                      \
+        if (f_col) F[o] = Fo;                                                                       \
+        if ((J) <= g_hi) G[o] = Go;                          /* global j <= j_max-1 (integration.c:84) */ \
+        o += pitch;                                                                                 \
+        if ((J) + 1 > jend) break;                                                                  \
+        fg_load3(US, u + o + pitch); fg_load3(VS, v + o + pitch);   /* row J+2 replaces row J-1 */  \
+    }
+    for (int j = j0;; j += 3) {
+        FG_STEP(ua, ub, uc, va, vb, vc, j)
+        FG_STEP(ub, uc, ua, vb, vc, va, j + 1)
+        FG_STEP(uc, ua, ub, vc, va, vb, j + 2)
+    }
+#undef FG_STEP
 }
 
 cudaError_t nsb_launch_fg(nsb_ctx* c, double dt, double gamma) {
     MomCoef m = make_mom(c, dt, gamma);
-    dim3 b(MB_X, MB_Y), g((c->g.ni + MB_X - 1) / MB_X, (c->g.nj + MB_Y - 1) / MB_Y);
+    dim3 b(FG_BX), g((c->g.ni + FG_BX - 1) / FG_BX, (c->g.nj + FG_ROWS - 1) / FG_ROWS);
     const int g_hi = c->wall_top ? c->g.nj - 1 : c->g.nj;
     if (c->use_recip) fg_kernel<true><<<g, b, 0, c->stream>>>(c->u, c->v, c->F, c->G, c->g.pitch, c->g.ni, c->g.nj, g_hi, m);
     else fg_kernel<false><<<g, b, 0, c->stream>>>(c->u, c->v, c->F, c->G, c->g.pitch, c->g.ni, c->g.nj, g_hi, m);
@@ -240,8 +304,16 @@ __device__ __forceinline__ void uv_red_store(StepRed* red, const double* out) {
 // interior column i = 1 sits on a 32-byte boundary, so cells (i, i+1) with odd i are one aligned double2 of every
 // array -- F, G, p, p one row up in, u, v out; 72 B in flight per thread and pass (r1: one cell per thread, five scalar
 // loads, a block per quarter row: 4.16 TB/s with 39 stall cycles per issue on the loads, profiles/r1j_ncu_summary.txt).
+#ifndef UV_THREADS
+#define UV_THREADS 256
+#endif
+#ifndef UV_UNROLL
+#define UV_UNROLL 2
+#endif
+#define UV_PRAGMA(x) _Pragma(#x)
+#define UV_UNROLL_PRAGMA(n) UV_PRAGMA(unroll n)
 template <bool RECIPD, bool UPDATE>
-__global__ void __launch_bounds__(256) update_uv_kernel(double* __restrict__ u, double* __restrict__ v,
+__global__ void __launch_bounds__(UV_THREADS) update_uv_kernel(double* __restrict__ u, double* __restrict__ v,
                                                          const double* __restrict__ F, const double* __restrict__ G,
                                                          const double* __restrict__ p, long long pitch, int ni,
                                                          int nj, MomCoef m, UvRedArgs ra) {
@@ -251,8 +323,8 @@ __global__ void __launch_bounds__(256) update_uv_kernel(double* __restrict__ u, 
     const long long ro = (long long)(j + NSB_ROW0) * pitch + NSB_COL0;
     const bool v_row = (j <= ra.v_hi);                           // global j <= j_max-1 (main.c:134)
     double mu = -1.0e300, mv = -1.0e300, sp = 0.0;
-#pragma unroll 2
-    for (int i = 1 + 2 * threadIdx.x; i <= ni; i += 2 * blockDim.x) {
+    UV_UNROLL_PRAGMA(UV_UNROLL)
+    for (int i = 1 + 2 * threadIdx.x; i <= ni; i += 2 * UV_THREADS) {
         const long long o = ro + i;
         const bool two = (i + 1 <= ni);                          // the second cell of the pair is an interior cell
         const double2 pc = *reinterpret_cast<const double2*>(p + o);
@@ -303,7 +375,7 @@ __global__ void __launch_bounds__(256) update_uv_kernel(double* __restrict__ u, 
         // that depends on the global band count only (slab.cuh)
         __threadfence();
         const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, gx = 1;
-        for (int b = warp; b < ra.n_chunks; b += 8) {
+        for (int b = warp; b < ra.n_chunks; b += UV_THREADS / 32) {
             const int r0 = b * ra.chunk_rows;
             const int rows = min(ra.chunk_rows, nj - r0);
             const double a = warp_ordered_max(ra.partials + (size_t)r0 * gx, rows * gx, lane);
@@ -370,8 +442,8 @@ cudaError_t nsb_launch_update_uv(nsb_ctx* c, double dt) {
                     (c->O.div_mode == NSB_DIV_AUTO && pow2(c->dx) && pow2(c->dy));
     double* p = c->pbuf[c->pcur];
     UvRedArgs ra = uv_red_args(c);
-    if (rd) update_uv_kernel<true, true><<<g, 256, 0, c->stream>>>(c->u, c->v, c->F, c->G, p, c->g.pitch, c->g.ni, c->g.nj, m, ra);
-    else update_uv_kernel<false, true><<<g, 256, 0, c->stream>>>(c->u, c->v, c->F, c->G, p, c->g.pitch, c->g.ni, c->g.nj, m, ra);
+    if (rd) update_uv_kernel<true, true><<<g, UV_THREADS, 0, c->stream>>>(c->u, c->v, c->F, c->G, p, c->g.pitch, c->g.ni, c->g.nj, m, ra);
+    else update_uv_kernel<false, true><<<g, UV_THREADS, 0, c->stream>>>(c->u, c->v, c->F, c->G, p, c->g.pitch, c->g.ni, c->g.nj, m, ra);
     return NSB_LAUNCHED(c, 1);
 }
 
@@ -379,7 +451,7 @@ cudaError_t nsb_launch_reduce_uvp(nsb_ctx* c) {
     MomCoef m = make_mom(c, 1.0, 0.0);
     dim3 g;
     uv_grid(c, g);
-    update_uv_kernel<true, false><<<g, 256, 0, c->stream>>>(c->u, c->v, c->F, c->G, c->pbuf[c->pcur], c->g.pitch,
+    update_uv_kernel<true, false><<<g, UV_THREADS, 0, c->stream>>>(c->u, c->v, c->F, c->G, c->pbuf[c->pcur], c->g.pitch,
                                                             c->g.ni, c->g.nj, m, uv_red_args(c));
     return NSB_LAUNCHED(c, 1);
 }
