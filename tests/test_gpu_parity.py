@@ -81,6 +81,33 @@ def test_bc_fg_rhs_update_bit_exact(ni, nj, a, b):
     s.close()
 
 
+@pytest.mark.parametrize("ni,nj,a,b", [(130, 9, 1.0, 1.0), (300, 301, 1.3, 0.7), (257, 257, 1.0, 1.0), (64, 2, 1.0, 0.3), (33, 1, 1.0, 1.0)])
+def test_fg_row_march_and_ieee_quotient_window(ni, nj, a, b):
+    """fg_kernel marches 3 rows per thread and carries the y-face fluxes from row to row (momentum.cu): row counts of
+    every remainder mod 3, one and two rows; with non power-of-two spacing the Laplacians divide by dx^2, dy^2 through
+    the refined reciprocal and fall back to the real division outside its window -- exact zeros, -0.0, denormals and
+    large values in u and v.  F and G bit for bit (the sign of zero included)."""
+    m = nsb()
+    s, P = _solver(m, i_max=ni, j_max=nj, a=a, b=b, Re=313.0, g_x=0.0, g_y=-0.5)
+    u, v = _rand(s.shape, 61), _rand(s.shape, 62)
+    i1, i2 = ni // 4, ni // 2
+    u[i1:i2, :] = 0.0; v[i1 + 2:i2 + 2, :] = 0.0
+    u[i1 + 1, :] = -0.0
+    u[i2 + 3, 1:] = 1e-310; v[i2 + 5, :] = -3e-320; u[i2 + 7, 1] = 4.9e-324
+    u[2, :] = 1e120; v[3, 1] = -1e140
+    s.upload(m.U, u); s.upload(m.V, v)
+    dx, dy = a / ni, b / nj
+    with np.errstate(all="ignore"):
+        for dt, gamma in ((0.0123, 0.41), (1e-3, 0.0)):
+            s.FG(dt, gamma)
+            F, G = np.zeros_like(u), np.zeros_like(u)
+            ob.lib().orc_FG(ob._ptr(F), ob._ptr(G), ob._ptr(u), ob._ptr(v), ni, nj, P.Re, P.g_x, P.g_y, dt, dx, dy, gamma)
+            assert np.all(np.isfinite(F)) and np.all(np.isfinite(G))
+            assert np.array_equal(s.download(m.F).view(np.int64), F.view(np.int64))
+            assert np.array_equal(s.download(m.G).view(np.int64), G.view(np.int64))
+    s.close()
+
+
 def test_layout_roundtrip_both_layouts():
     m = nsb()
     s, P = _solver(m, i_max=45, j_max=70)
