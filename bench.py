@@ -352,8 +352,8 @@ def main():
         nj_local = nj
     else:
         # one slab per process; NCCL only carries the 256-byte slab descriptors, once.
-        # 124-row bands: 124 + 11 rows are 17 blocks of 8 steps of the two-iteration pass (128 would need an 18th)
-        ch = args.chunk_rows or 124
+        # band height: planned by the library for the slab height unless given (8192-row slabs: 124 rows)
+        ch = args.chunk_rows
         s = m.SlabSolver(P, rank, world, m.torch_all_gather(), device=local, chunk_rows=ch, pass_k=args.pass_k)
         nj_local = s.nj
     plan = s.sor_plan()

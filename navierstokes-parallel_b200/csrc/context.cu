@@ -177,7 +177,14 @@ int nsb_create_slab_internal(const nsb_params* P, const nsb_options* opt, int ra
         c->g.nj = P->j_max; c->j_lo = 0;
     } else {
         // the chunk height is part of the decomposition: fixed before the rows are dealt out
-        int ch = c->O.sor_chunk_rows > 0 ? ((c->O.sor_chunk_rows + 1) & ~1) : 124;   // 124 + 11 rows = 17 blocks of the two-iteration pass
+        int ch;
+        if (c->O.sor_chunk_rows > 0) ch = (c->O.sor_chunk_rows + 1) & ~1;
+        else {
+            // planned for the slab height (8192-row slabs: 124 rows -- 124 + 11 rows = 17 blocks of the two-iteration pass)
+            int k = 0;
+            ch = nsb_sor_preplan_slabs(c, P->i_max, P->j_max, world, &k);
+            if (c->O.sor_pass_k == 0) c->O.sor_pass_k = k;     // the iterations per pass this height was chosen for
+        }
         if (ch < 16) ch = 16;
         c->O.sor_chunk_rows = ch;
         int nj = 0;

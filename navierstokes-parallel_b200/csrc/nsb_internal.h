@@ -221,6 +221,7 @@ int nsb_sor_resident_supported(const nsb_ctx* c);
 cudaError_t nsb_launch_sor_resident(nsb_ctx* c, int max_it, int check);
 
 void nsb_sor_plan(nsb_ctx* c);
+int nsb_sor_preplan_slabs(const nsb_ctx* c, int ni, int j_max, int world, int* k_out);   // band height of a y-slab decomposition (before nsb_sor_plan)
 // output.cu: field dumps in the reference's format for the n slabs cs[0..n-1] of one decomposition (rank order)
 int nsb_out_run(nsb_ctx** cs, int n, double t, const char* prefix, int async);
 int nsb_out_wait(nsb_ctx* c0);

@@ -1249,9 +1249,9 @@ extern "C" int nsb_plan_sor(int ni, int nj, long long slots1, long long slots2, 
     return two ? 2 : 1;
 }
 
-void nsb_sor_plan(nsb_ctx* c) {
-    const int ni = c->g.ni, nj = c->g.nj;
-    // function attributes are per device: set them for the device of every context that is planned
+// Resident warps of the persistent sweep kernels on this context's device (slots[1], slots[2]: one / two iterations per
+// pass).  Function attributes are per device: they are set for the device of every context that is planned.
+static void sor_slots(const nsb_ctx* c, long long (&slots)[3]) {
     for (int v = 0; v < 4; v++) {
         cudaFuncSetAttribute((const void*)sor_stream_fn(v & 1, v & 2), cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES(1));
         cudaFuncSetAttribute((const void*)sor_persist_fn(v & 1, v & 2, 1), cudaFuncAttributeMaxDynamicSharedMemorySize, SOR_SMEM_BYTES(1));
@@ -1260,19 +1260,49 @@ void nsb_sor_plan(nsb_ctx* c) {
         // carve-out fitted ONE block: 5 warps per SM, profiles/r2w)
         cudaFuncSetAttribute((const void*)sor_persist_fn(v & 1, v & 2, 2), cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     }
-    c->n_strips = (ni + NSB_STRIP_COLS - 1) / NSB_STRIP_COLS;
-    long long slots[3] = {0, 0, 0};
+    slots[0] = 0;
     for (int k = 1; k <= 2; k++) {
         int bps = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, (const void*)sor_persist_fn(c->use_recip, c->world > 1, k), SOR_KTHREADS(k), SOR_SMEM_BYTES(k));
         if (bps < 1) bps = 1;
         slots[k] = (long long)c->sm_count * bps * SOR_KWARPS(k);
     }
-    int want = c->O.sor_pass_k >= 1 && c->O.sor_pass_k <= NSB_SOR_KMAX ? c->O.sor_pass_k : 0;      // 0 = by the model
-    {
-        const char* env = getenv("NSB_SOR_K");
-        if (env && atoi(env) >= 1 && atoi(env) <= NSB_SOR_KMAX) want = atoi(env);
-    }
+}
+
+// Iterations per pass the caller asked for: nsb_options.sor_pass_k, overridden by NSB_SOR_K; 0 = by the model.
+static int sor_wanted_k(const nsb_ctx* c) {
+    int want = c->O.sor_pass_k >= 1 && c->O.sor_pass_k <= NSB_SOR_KMAX ? c->O.sor_pass_k : 0;
+    const char* env = getenv("NSB_SOR_K");
+    if (env && atoi(env) >= 1 && atoi(env) <= NSB_SOR_KMAX) want = atoi(env);
+    return want;
+}
+
+// y-slabs: the band height is part of the decomposition, so it is planned BEFORE the rows are dealt out, for a slab of
+// ceil(j_max / world) rows -- the same arithmetic on every rank (same grid, same world size, same kind of GPU).  r2 used
+// 124-row bands for every decomposition: right for 8192-row slabs, but 16384^2 on 8 GPUs (2048-row slabs, 17 bands) then
+// left the two-iteration pass with 2 tasks per warp and the model fell back to one iteration per pass
+// (profiles/r3m_scale_summary.txt: 154 us per iteration, 0.56 of 8 x the single GPU).
+// Returns the band height; *k_out = iterations per pass that go with it.
+int nsb_sor_preplan_slabs(const nsb_ctx* c, int ni, int j_max, int world, int* k_out) {
+    long long slots[3];
+    sor_slots(c, slots);
+    const int nj_slab = (j_max + world - 1) / world;
+    const int want = sor_wanted_k(c);
+    int rows = 0, k = want;
+    if (k == 0) k = nsb_plan_sor(ni, nj_slab, slots[1], slots[2], c->use_recip ? 1 : 0, &rows);
+    else rows = plan_chunk_rows(ni, nj_slab, slots[k], c->use_recip ? 1 : 0, k, NULL);
+    if (rows < 16) rows = 16;
+    while (rows > 16 && (j_max + rows - 1) / rows < world) rows -= 2;      // every slab needs a band
+    if (k_out) *k_out = k;
+    return rows;
+}
+
+void nsb_sor_plan(nsb_ctx* c) {
+    const int ni = c->g.ni, nj = c->g.nj;
+    c->n_strips = (ni + NSB_STRIP_COLS - 1) / NSB_STRIP_COLS;
+    long long slots[3];
+    sor_slots(c, slots);
+    const int want = sor_wanted_k(c);
     int rows = 0, k = want;
     if (c->O.sor_chunk_rows > 0) {
         rows = (c->O.sor_chunk_rows + 1) & ~1;

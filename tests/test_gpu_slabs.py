@@ -71,18 +71,29 @@ def test_whole_run_equals_single_slab_and_oracle(world):
 
 
 def test_slabs_at_default_chunk_and_nonsquare_box():
-    """124-row bands (the default chunk height of a decomposition), ragged last band, dx != dy, gravity, oscillating lid."""
+    """124-row bands (what the planner picks for 8192-row slabs), ragged last band, dx != dy, gravity, oscillating lid;
+    then the band height the library plans for THIS decomposition (nsb_sor_preplan_slabs): other bands, so the residual
+    is summed in another order -- the fields are the same bits as long as the iteration counts agree."""
     m = nsb()
     P = _params(m, i_max=130, j_max=500, a=1.0, b=2.5, T=0.2, max_it=60, problem=2, f=3.0, g_x=0.3, g_y=-0.2)
     with m.Solver(P, sor_engine=m.SOR_STREAM, chunk_rows=124) as s:
         log1, _ = s.run(max_steps=3)
         f1 = [s.download(f) for f in (m.U, m.V, m.P)]
-    with m.Group(P, [0, 0, 0]) as g:
+    with m.Group(P, [0, 0, 0], chunk_rows=124) as g:
         assert [x["nj"] for x in g.slabs()] == [248, 124, 128]
         logg, _ = g.run(max_steps=3)
         fg = [g.download(f) for f in (m.U, m.V, m.P)]
     assert [(x["sor_iters"], x["dt"], x["res"]) for x in logg] == [(x["sor_iters"], x["dt"], x["res"]) for x in log1]
     for a, b in zip(fg, f1):
+        assert np.array_equal(a[1:-1, 1:-1], b[1:-1, 1:-1])
+    with m.Group(P, [0, 0, 0]) as g:
+        nj = [x["nj"] for x in g.slabs()]
+        assert sum(nj) == 500 and min(nj) >= 16
+        logd, _ = g.run(max_steps=3)
+        fd = [g.download(f) for f in (m.U, m.V, m.P)]
+    assert [x["sor_iters"] for x in logd] == [x["sor_iters"] for x in log1]
+    assert np.allclose([x["res"] for x in logd], [x["res"] for x in log1], rtol=1e-12, atol=0.0)
+    for a, b in zip(fd, f1):
         assert np.array_equal(a[1:-1, 1:-1], b[1:-1, 1:-1])
 
 
