@@ -275,10 +275,10 @@ int nsb_create_slab_internal(const nsb_params* P, const nsb_options* opt, int ra
     CUC(cudaMalloc((void**)&c->d_partials, (size_t)np * sizeof(double)));
     CUC(cudaMalloc((void**)&c->d_partials2, (size_t)2 * NSB_SOR_KMAX * c->n_partials * sizeof(double)));
     CUC(cudaMalloc((void**)&c->d_bandvals2, (size_t)2 * NSB_SOR_KMAX * (c->n_chunks + 1) * sizeof(double)));
-    CUC(cudaMalloc((void**)&c->d_claim, 8 * sizeof(unsigned long long)));
+    CUC(cudaMalloc((void**)&c->d_claim, (8 + 2 * (size_t)c->n_chunks) * sizeof(unsigned long long)));   // [0] claim, [1..4] pass tickets, [8..] band tickets by pass parity
     CUC(cudaMalloc((void**)&c->d_done, (size_t)c->n_partials * sizeof(unsigned long long)));
     CUC(cudaMemsetAsync(c->d_partials2, 0, (size_t)2 * NSB_SOR_KMAX * c->n_partials * sizeof(double), c->stream));
-    CUC(cudaMemsetAsync(c->d_claim, 0, 8 * sizeof(unsigned long long), c->stream));
+    CUC(cudaMemsetAsync(c->d_claim, 0, (8 + 2 * (size_t)c->n_chunks) * sizeof(unsigned long long), c->stream));
     CUC(cudaMemsetAsync(c->d_done, 0, (size_t)c->n_partials * sizeof(unsigned long long), c->stream));
     c->n_red_partials = 3 * 4 * c->g.nj + 64;
     CUC(cudaMalloc((void**)&c->d_red_partials, (size_t)c->n_red_partials * sizeof(double)));

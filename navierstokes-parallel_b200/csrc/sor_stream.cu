@@ -207,7 +207,7 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
 }
 
 // One thread: closes iteration `it` with the global sum of r^2.
-__device__ __forceinline__ void sor_close_iteration(double total, SorCtl* ctl, int it, long long cells) {
+__device__ __forceinline__ void sor_close_iteration(double total, SorCtl* ctl, int it, long long cells, bool publish = true) {
     double res = sqrt(total / (double)cells);              // main.cu:588
     ctl->sum_r2 = total;
     ctl->res = res;
@@ -215,7 +215,7 @@ __device__ __forceinline__ void sor_close_iteration(double total, SorCtl* ctl, i
     __threadfence();                                        // `converged` is visible before `iters` says "closed"
     *((volatile int*)&ctl->iters) = it + 1;
     __threadfence();
-    sor_publish(ctl);
+    if (publish) sor_publish(ctl);
 }
 
 // Per-lane geometry, fixed for the whole task.
@@ -929,31 +929,28 @@ __device__ __forceinline__ bool spin_gpu_ge(const unsigned long long* flag, unsi
     return true;
 }
 
-// Band sums of one sub-iteration's partials (one band = one chunk of rows, strips in a fixed order), by one warp.
-// 16 bands at a time, so that 16 loads per lane are in flight: one band after the other
-// (an L2 round trip each) took ~0.5 us per band, 40 us for the 86 bands of 2048^2 -- as long as
-// the iteration itself, and iteration n+2 waits for this closing (ncu source page, 2048^2:
-// half of all warp samples sat in the `iters` poll).  Per band the additions are those
-// of warp_ordered_sum (lane-strided partials in q order, then the butterfly): same bits.
-__device__ __forceinline__ void sor_band_sums(const double* part, double* bandvals, int n_chunks, int n_strips, int lane) {
-    for (int b0 = 0; b0 < n_chunks; b0 += 16) {
-        double sb[16];
-#pragma unroll
-        for (int u = 0; u < 16; u++) sb[u] = 0.0;
-        for (int q = lane; q < n_strips; q += 32) {
-#pragma unroll
-            for (int u = 0; u < 16; u++)
-                if (b0 + u < n_chunks) sb[u] += __ldcg(part + (size_t)(b0 + u) * n_strips + q);
-        }
-#pragma unroll
-        for (int u = 0; u < 16; u++) sb[u] = warp_sum(sb[u]);
-        if (lane == 0) {
-#pragma unroll
-            for (int u = 0; u < 16; u++)
-                if (b0 + u < n_chunks) bandvals[b0 + u] = sb[u];
-        }
-    }
+#ifdef SOR_TASK_TIMING
+// Developer build (tools/task_timing.py): where a task's time goes, summed over all tasks of a launch (lane 0, ns).
+// [0] claim  [1] closed-pass / convergence word  [2] 3 x 3 flags  [3] geometry, buffers, neighbour flags  [4] the march
+// [5] partials, fence, done flag, ticket  [6] closing a pass (the closing warps only)  [7] tasks
+__device__ unsigned long long g_task_t[16];   // [8..10] march time of interior / wall-chunk / edge-strip tasks, [11..13] their counts
+extern "C" void nsb_debug_task_timing(unsigned long long* out) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, g_task_t, sizeof g_task_t);
+    unsigned long long z[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    cudaMemcpyToSymbol(g_task_t, z, sizeof z);
 }
+#define SOR_TT(i)                                                                          \
+    do {                                                                                   \
+        if (lane == 0) {                                                                   \
+            const unsigned long long now__ = global_timer_ns();                            \
+            atomicAdd(&g_task_t[i], now__ - tt_prev);                                      \
+            tt_prev = now__;                                                               \
+        }                                                                                  \
+    } while (0)
+#else
+#define SOR_TT(i) do { } while (0)
+#endif
 
 template <bool RECIP, bool MULTI, int K>
 // registers: 168 (3 blocks of 4 warps) for one iteration per pass; two: 168 with the RHS ring in shared memory, 255 without (2 blocks of 4)
@@ -977,11 +974,18 @@ __global__ void __maxnreg__(K == 1 ? 168 : (SOR_RS(K) ? 168 : 255)) sor_persist_
     }
     __syncwarp();
 
+#ifdef SOR_TASK_TIMING
+    unsigned long long tt_prev = global_timer_ns();
+#endif
+    // The first task is claimed here; every further one while the finished task's stores drain (below): the claim's
+    // round trip to L2 (~1 us) overlaps the fence instead of preceding the next task.  (Claiming BEFORE the march, one
+    // task ahead, kept the claimed id live across the hot loop and was slower: 2048^2 32 -> 42 us)
+    unsigned long long id = 0;
+    if (lane == 0) id = atomicAdd(pa.claim, 1ull);
+    id = __shfl_sync(FULLM, id, 0);
     for (;;) {
-        unsigned long long id = 0;
-        if (lane == 0) id = atomicAdd(pa.claim, 1ull);
-        id = __shfl_sync(FULLM, id, 0);
         if (id >= total) break;
+        SOR_TT(0);
         const int ps = (int)(id / (unsigned long long)a.n_tasks);                 // pass
         const int task = (int)(id - (unsigned long long)ps * (unsigned long long)a.n_tasks);
         const int it_first = a.it + ps * K;                                        // global number of this pass's first iteration
@@ -997,44 +1001,46 @@ __global__ void __maxnreg__(K == 1 ? 168 : (SOR_RS(K) ? 168 : 255)) sor_persist_
             chunk = (chunk & 1) ? a.n_chunks - 1 - (chunk >> 1) : (chunk >> 1);
         const int tslot = chunk * a.n_strips + strip;      // index of this task's flag and partials
 
-        // ---- may this pass run?  pass ps-2 must be closed, and nothing before may have converged
-        // (the wait also keeps the double-buffered partials and the 4 tickets of pass ps-2 / ps-4 safe,
-        //  so it does not depend on `check`)
+        // ---- may this task run?  (1) pass ps-2 must be closed and nothing before may have converged (lane 9 reads
+        // {iters, converged}, one 64-bit word; the wait also keeps the double-buffered partials, band values and tickets
+        // of pass ps-2 safe, so it does not depend on `check`); (2) the 3 x 3 neighbourhood of the previous pass must be
+        // done (lanes 0 .. 8, one flag each).  ONE acquire load per round serves both: the two used to be dependent L2
+        // round trips, 0.8 + 1.5 us per task (profiles/r3s_task_timing.txt).  A converged solve stops the task before it
+        // could wait for flags that never come: tasks of pass ps-1 that saw the convergence never ran.
         int stop = 0;
         {
-            if (lane == 0) {
-                // {iters, converged} are adjacent: ONE 64-bit acquire load per task reads both (two dependent
-                // L2 round trips per task were ~2 % of the sweep with the convergence test on)
-                const unsigned long long* word = reinterpret_cast<const unsigned long long*>(&a.ctl->iters);
-                unsigned long long w = ld_acquire_gpu(word);
-                if (ps >= 2 && !pa.noclose) {
-                    const unsigned long long t0 = global_timer_ns();
-                    while ((int)(unsigned)(w & 0xffffffffull) < it_first - K) {
-                        if (a.check && (unsigned)(w >> 32)) break;                      // nothing closes after convergence
-                        if (*((volatile int*)a.err) || global_timer_ns() - t0 > spin_timeout_ns(a.err)) { *((volatile int*)a.err) = 1; stop = 1; break; }
-                        __nanosleep(64);
-                        w = ld_acquire_gpu(word);
-                    }
+            const int cc = chunk + lane / 3 - 1, ss = strip + lane % 3 - 1;
+            const bool is_ctl = (lane == 9);
+            const bool is_flag = ps > 0 && lane < 9 && cc >= 0 && cc < a.n_chunks && ss >= 0 && ss < a.n_strips;
+            const unsigned long long* addr = is_ctl ? reinterpret_cast<const unsigned long long*>(&a.ctl->iters)
+                                                    : pa.done + (is_flag ? (size_t)cc * a.n_strips + ss : (size_t)0);
+            const unsigned long long want = pa.flag_base + (unsigned long long)ps;
+            const bool wait_close = (ps >= 2 && !pa.noclose);
+            bool pending = is_ctl || is_flag;
+            unsigned long long t0 = 0;
+            for (int round = 0;; round++) {
+                int st = 0;
+                if (pending) {
+                    const unsigned long long w = ld_acquire_gpu(addr);
+                    if (is_ctl) {
+                        if (a.check && (unsigned)(w >> 32)) st = 1;                       // nothing closes after convergence
+                        else if (!wait_close || (int)(unsigned)(w & 0xffffffffull) >= it_first - K) pending = false;
+                    } else if (w >= want) pending = false;
                 }
-                if (a.check && (unsigned)(w >> 32)) stop = 1;
+                if (__any_sync(FULLM, st)) { stop = 1; break; }
+                if (!__any_sync(FULLM, pending)) break;
+                if (round == 0) t0 = global_timer_ns();
+                int bad = 0;
+                if (lane == 0 && (*((volatile int*)a.err) || global_timer_ns() - t0 > spin_timeout_ns(a.err))) { *((volatile int*)a.err) = 1; bad = 1; }
+                if (__any_sync(FULLM, bad)) { stop = 1; break; }
+                __nanosleep(64);
             }
-            stop = __shfl_sync(FULLM, stop, 0);
         }
         if (stop) break;
+        SOR_TT(1);
+        asm volatile("fence.proxy.async;" ::: "memory");       // other warps' generic stores -> this warp's TMA reads
 
-        // ---- wait for the 3 x 3 neighbourhood of the previous pass
-        if (ps > 0) {
-            int ok = 1;
-            if (lane < 9) {
-                const int cc = chunk + lane / 3 - 1, ss = strip + lane % 3 - 1;
-                if (cc >= 0 && cc < a.n_chunks && ss >= 0 && ss < a.n_strips)
-                    ok = spin_gpu_ge(pa.done + (size_t)cc * a.n_strips + ss, pa.flag_base + (unsigned long long)ps, a.err) ? 1 : 0;
-            }
-            ok = __all_sync(FULLM, ok);
-            if (!ok) break;
-            asm volatile("fence.proxy.async;" ::: "memory");   // other warps' generic stores -> this warp's TMA reads
-        }
-
+        SOR_TT(2);
         const int bi = (pa.buf0 + ps) % 3;                  // buffer this pass reads
         const int bo = (bi + 1) % 3;                        // ... and writes
 
@@ -1069,7 +1075,19 @@ __global__ void __maxnreg__(K == 1 ? 168 : (SOR_RS(K) ? 168 : 255)) sor_persist_
         }
 
         double accs[K];
+        SOR_TT(3);
+#ifdef SOR_TASK_TIMING
+        const unsigned long long tt_m0 = global_timer_ns();
+#endif
         sor_task<RECIP, K>(t, a.k, lg, edge_strip, full_par, empty_par, accs);
+#ifdef SOR_TASK_TIMING
+        if (lane == 0) {
+            const int kind = (strip == 0 || strip == a.n_strips - 1) ? 2 : ((chunk == 0 || chunk == a.n_chunks - 1) ? 1 : 0);
+            atomicAdd(&g_task_t[8 + kind], global_timer_ns() - tt_m0);
+            atomicAdd(&g_task_t[11 + kind], 1ull);
+        }
+#endif
+        SOR_TT(4);
         double* part = pa.partials2 + (size_t)(ps & 1) * NSB_SOR_KMAX * a.n_tasks;
 #pragma unroll
         for (int q = 0; q < K; q++) {
@@ -1078,6 +1096,8 @@ __global__ void __maxnreg__(K == 1 ? 168 : (SOR_RS(K) ? 168 : 255)) sor_persist_
         }
 
         // ---- publish: rows and partials are out
+        unsigned long long next_id = 0;
+        if (lane == 0) next_id = atomicAdd(pa.claim, 1ull);      // the next task of this warp, in flight during the fence
         __threadfence();
         __syncwarp();
         unsigned long long tk = 0;
@@ -1089,23 +1109,43 @@ __global__ void __maxnreg__(K == 1 ? 168 : (SOR_RS(K) ? 168 : 255)) sor_persist_
                 if (t.push_up()) st_release_sys(a.up_flag + strip, a.seq + (unsigned long long)ps + 1ull);
             }
         }
+        // Two-level closing.  The LAST task of a band (chunk) sums that band's partials, in the fixed order of the
+        // per-iteration kernel (warp_ordered_sum over the strips), and only then takes a ticket of the pass; the last
+        // BAND closes the pass.  (r2: one ticket per task, and the closing warp summed all n_tasks partials of the pass --
+        // 25-90 us of dependent L2 round trips per pass, on one warp, with the closes of successive passes in series: at
+        // 2048^2 that chain, not the sweep, set the pace of an iteration; profiles/r3s_task_timing.txt.)
+        // The band tickets and band values are double-buffered by pass parity: no task of pass ps+2 starts before pass ps
+        // is closed.
+        unsigned long long* band_ticket = pa.claim + 8 + (size_t)(ps & 1) * a.n_chunks + chunk;
         if (lane == 0) {
             st_release_gpu(pa.done + tslot, pa.flag_base + (unsigned long long)ps + 1ull);
-            tk = atomicAdd(pa.claim + 1 + (ps & 3), 1ull);
+            tk = atomicAdd(band_ticket, 1ull);
         }
         tk = __shfl_sync(FULLM, tk, 0);
-        if (tk == (unsigned long long)a.n_tasks - 1ull) {
-            // this warp closes pass `ps`: band sums in the fixed order of the per-iteration kernel, per sub-iteration.
-            // The band values are double-buffered by pass parity: the closer of pass ps-1 may still be reading its own.
+        id = __shfl_sync(FULLM, next_id, 0);
+        SOR_TT(5);
+#ifdef SOR_TASK_TIMING
+        if (lane == 0) atomicAdd(&g_task_t[7], 1ull);
+#endif
+        if (tk != (unsigned long long)a.n_strips - 1ull) continue;
+        double* bands = pa.bandvals2 + (size_t)(ps & 1) * NSB_SOR_KMAX * (a.n_chunks + 1);
+        __threadfence();
+        if (lane == 0) *band_ticket = 0ull;
+        if (!pa.noclose) {
+#pragma unroll
+            for (int q = 0; q < K; q++) {
+                const double v = warp_ordered_sum(part + (size_t)q * a.n_tasks + (size_t)chunk * a.n_strips, a.n_strips, lane);
+                if (lane == 0) bands[(size_t)q * (a.n_chunks + 1) + chunk] = v;
+            }
+        }
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) tk = atomicAdd(pa.claim + 1 + (ps & 3), 1ull);
+        tk = __shfl_sync(FULLM, tk, 0);
+        if (tk == (unsigned long long)a.n_chunks - 1ull) {
+            // this warp closes pass `ps`: the bands in the fixed global order, per sub-iteration
             __threadfence();
             if (lane == 0) pa.claim[1 + (ps & 3)] = 0ull;
-            double* bands = pa.bandvals2 + (size_t)(ps & 1) * NSB_SOR_KMAX * (a.n_chunks + 1);
-            if (!pa.noclose) {
-#pragma unroll
-                for (int q = 0; q < K; q++)
-                    sor_band_sums(part + (size_t)q * a.n_tasks, bands + (size_t)q * (a.n_chunks + 1), a.n_chunks, a.n_strips, lane);
-            }
-            __threadfence();
             __syncwarp();
             // iterations close in order; nothing closes (and no reduction round is spent) after the one
             // that converged -- every rank sees the same residual bits, so every rank decides the same
@@ -1134,12 +1174,15 @@ __global__ void __maxnreg__(K == 1 ? 168 : (SOR_RS(K) ? 168 : 255)) sor_persist_
                 }
                 int conv = 0;
                 if (lane == 0) {
-                    sor_close_iteration(tot, a.ctl, it_first + q, a.k.cells);
+                    // (no copy to the pinned-host twin: nobody polls it during this kernel, nsb_ph_sor_end reads the
+                    //  device block after the launch -- a system-scope fence per iteration is not free)
+                    sor_close_iteration(tot, a.ctl, it_first + q, a.k.cells, false);
                     conv = (a.check && a.ctl->converged) ? 1 : 0;
                 }
                 skip = __shfl_sync(FULLM, conv, 0);          // the later sub-iterations of a converged pass are not closed
             }
             __syncwarp();
+            SOR_TT(6);
         }
     }
 }
@@ -1445,7 +1488,7 @@ cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int k, int n_pass, int it0, int c
     // at most two passes are in flight at any time: more warps than that would only poll flags
     const long long useful = (2LL * a.n_tasks + kw - 1) / kw + 1;
     if (blocks > useful) blocks = useful;
-    cudaError_t e = cudaMemsetAsync(c->d_claim, 0, 8 * sizeof(unsigned long long), c->stream);
+    cudaError_t e = cudaMemsetAsync(c->d_claim, 0, (8 + 2 * (size_t)c->n_chunks) * sizeof(unsigned long long), c->stream);   // claim counter, pass tickets, band tickets
     if (e != cudaSuccess) return e;
     kern<<<(int)blocks, SOR_KTHREADS(k), SOR_SMEM_BYTES(k), c->stream>>>(pa);
     return NSB_LAUNCHED(c, 1);
