@@ -83,7 +83,9 @@ typedef struct nsb_options {
     int device;          /* CUDA device ordinal                                                */
     int div_mode;        /* NSB_DIV_*                                                           */
     int sor_engine;      /* NSB_SOR_*                                                           */
-    int sor_chunk_rows;  /* rows per streaming chunk (0 = auto)                                 */
+    int sor_chunk_rows;  /* rows per streaming chunk (0 = auto: planned for the grid; with y-slabs it is also the band
+                            height of the decomposition, planned for a slab of ceil(j_max / world) rows -- the same on
+                            every rank; nsb_slab_info / nsb_sor_plan_info report what was chosen)              */
     int sor_check_batch; /* SOR launches the host may run ahead of the device (0 = auto, 24)      */
     void* stream;        /* cudaStream_t to run on (NULL = library creates its own)              */
     int sor_pass_k;      /* SOR iterations per pass over HBM of the persistent sweep: 1 = one, 2 = two (temporal
