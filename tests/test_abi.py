@@ -130,6 +130,32 @@ def test_chunk_height_model_of_the_persistent_sweep():
     assert f(8192, 8, 1776, 1) == 10 and f(5, 250, 1776, 1) == 10 and f(100, 100, 0, 1) >= 10
 
 
+def test_joint_plan_of_iterations_per_pass_and_chunk_height():
+    """nsb_plan_sor (host arithmetic): iterations per pass AND chunk height for a grid -- also what a y-slab decomposition
+    plans its band height with, applied to one slab of ceil(j_max / world) rows (nsb_sor_preplan_slabs).  B200: 1776 / 1184
+    resident warps with one / two iterations per pass.  Measured counterparts: profiles/r2n_k2_sweep.txt (squares),
+    profiles/r3n_rect_probe.txt (slab shapes: 16384 x 2048 planned 109 us per iteration, fixed 124-row bands 134-138)."""
+    L = nsb().lib()
+    f = L.nsb_plan_sor
+    f.restype = C.c_int
+    f.argtypes = [C.c_int, C.c_int, C.c_longlong, C.c_longlong, C.c_int, C.POINTER(C.c_int)]
+
+    def plan(ni, nj, recip=1):
+        rows = C.c_int()
+        k = f(ni, nj, 1776, 1184, recip, C.byref(rows))
+        return k, rows.value
+
+    assert plan(8192, 8192) == (2, 124)             # the headline grid; also one slab of the weak-scaling runs
+    assert plan(16384, 16384) == (2, 124)
+    assert plan(16384, 2048) == (2, 68)             # 16384^2 on 8 GPUs
+    assert plan(16384, 4096) == (2, 122)            # ... on 4
+    assert plan(2048, 2048) == (1, 22) and plan(4096, 4096)[0] == 1      # one iteration per pass below ~5000^2
+    assert plan(8191, 8191, recip=0)[0] == 1        # IEEE division: instruction bound, one iteration per pass
+    for ni, nj in ((300, 8), (5, 5000), (20000, 64)):
+        k, rows = plan(ni, nj)
+        assert k in (1, 2) and 10 <= rows <= 128 and rows % 2 == 0
+
+
 def test_output_formatter_equals_printf():
     """output.cu formats "%.5f" in exact integer arithmetic (host code of libnsb200.so, no GPU needed): it must produce
     printf's bytes -- round half to even on the exact binary value -- for field-like values, exact ties (k/64),
