@@ -892,7 +892,10 @@ struct SorPersistArgs {
     int n_pass;                      // passes of K iterations each
     int noclose;                     // replay of an iteration that is already closed: do not close again
     int wait_first;                  // y-slabs: pass 0 reads halo rows pushed by the previous launch (epoch s.seq)
-    unsigned long long* claim;       // [0] task counter, [1..4] tickets of passes mod 4
+    unsigned long long* claim;       // [0] task counter, [1..4] tickets of passes mod 4, [5] task counter of the edge strips
+                                     // (edge_sms > 0), [8 ..] band tickets by pass parity
+    int edge_sms;                    // > 0: the tasks of the first and the last strip are claimed from a queue of their own,
+                                     // which the warps of SMs 0 .. edge_sms-1 serve first (sor_claim)
     unsigned long long* done;        // [n_tasks] epoch of the last pass the task finished
     unsigned long long flag_base;    // epoch of "before pass 0 of this launch"
     double* partials2;               // [2][NSB_SOR_KMAX][n_tasks]
@@ -929,6 +932,33 @@ __device__ __forceinline__ bool spin_gpu_ge(const unsigned long long* flag, unsi
     return true;
 }
 
+// ---- claiming tasks.  One queue: id = pass * n_tasks + chunk * n_strips + strip.  Two queues (edge_sms > 0): the first
+// and the last strip -- whose tasks run bodies of their own (lane-masked / general edge body), rarely executed and
+// therefore cold in the 32 KB instruction cache whenever a warp next to the interior bodies runs them: 0.30 against 0.14
+// stall samples per instruction, and the interior warps of that SM miss too (profiles/r3v_task_kinds.txt) -- have a
+// queue of their own (bit 63 of the returned id), served first by the warps of SMs 0 .. edge_sms-1, which then run nothing
+// else; the other SMs serve the interior queue first.  Within a queue tasks are claimed in (pass, chunk) order, a claimed
+// task is held by a resident warp and waits only for tasks of earlier passes: no deadlock.  Lane 0 only.
+#define SOR_EDGE_QUEUE (1ull << 63)
+#define SOR_NO_TASK (~0ull)
+__device__ __forceinline__ unsigned long long sor_claim(const SorPersistArgs& pa, bool prefer_edge, unsigned long long total_main,
+                                                        unsigned long long total_edge) {
+    if (pa.edge_sms <= 0) {
+        const unsigned long long id = atomicAdd(pa.claim, 1ull);
+        return id < total_main ? id : SOR_NO_TASK;
+    }
+    if (prefer_edge) {
+        unsigned long long id = atomicAdd(pa.claim + 5, 1ull);
+        if (id < total_edge) return id | SOR_EDGE_QUEUE;
+        id = atomicAdd(pa.claim, 1ull);
+        return id < total_main ? id : SOR_NO_TASK;
+    }
+    unsigned long long id = atomicAdd(pa.claim, 1ull);
+    if (id < total_main) return id;
+    id = atomicAdd(pa.claim + 5, 1ull);
+    return id < total_edge ? (id | SOR_EDGE_QUEUE) : SOR_NO_TASK;
+}
+
 #ifdef SOR_TASK_TIMING
 // Developer build (tools/task_timing.py): where a task's time goes, summed over all tasks of a launch (lane 0, ns).
 // [0] claim  [1] closed-pass / convergence word  [2] 3 x 3 flags  [3] geometry, buffers, neighbour flags  [4] the march
@@ -959,7 +989,17 @@ __global__ void __maxnreg__(K == 1 ? 168 : (SOR_RS(K) ? 168 : 255)) sor_persist_
     const SorStreamArgs& a = pa.s;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned FULLM = 0xffffffffu;
-    const unsigned long long total = (unsigned long long)pa.n_pass * (unsigned long long)a.n_tasks;
+    // tasks per pass of the main queue / of the edge-strip queue (sor_claim)
+    const int per_main = pa.edge_sms > 0 ? (a.n_strips - 2) * a.n_chunks : a.n_tasks;
+    const int per_edge = pa.edge_sms > 0 ? 2 * a.n_chunks : 0;
+    const unsigned long long total = (unsigned long long)pa.n_pass * (unsigned long long)per_main;
+    const unsigned long long total_edge = (unsigned long long)pa.n_pass * (unsigned long long)per_edge;
+    bool prefer_edge = false;
+    if (pa.edge_sms > 0) {
+        unsigned int smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        prefer_edge = (int)smid < pa.edge_sms;
+    }
     unsigned char* ring = smem_raw + warp * SOR_WARP_SMEM(K);
     const uint32_t bar_base = smem_u32(smem_raw + SOR_KWARPS(K) * SOR_WARP_SMEM(K) + warp * SOR_BAR_BYTES);
     // The mbarriers are initialised once and live across the tasks of this warp.  Per task and stage
@@ -981,16 +1021,30 @@ __global__ void __maxnreg__(K == 1 ? 168 : (SOR_RS(K) ? 168 : 255)) sor_persist_
     // round trip to L2 (~1 us) overlaps the fence instead of preceding the next task.  (Claiming BEFORE the march, one
     // task ahead, kept the claimed id live across the hot loop and was slower: 2048^2 32 -> 42 us)
     unsigned long long id = 0;
-    if (lane == 0) id = atomicAdd(pa.claim, 1ull);
+    if (lane == 0) id = sor_claim(pa, prefer_edge, total, total_edge);
     id = __shfl_sync(FULLM, id, 0);
     for (;;) {
-        if (id >= total) break;
+        if (id == SOR_NO_TASK) break;
         SOR_TT(0);
-        const int ps = (int)(id / (unsigned long long)a.n_tasks);                 // pass
-        const int task = (int)(id - (unsigned long long)ps * (unsigned long long)a.n_tasks);
+        int ps, strip, chunk;                                                       // pass, strip, chunk of the claimed task
+        if (pa.edge_sms <= 0) {
+            ps = (int)(id / (unsigned long long)a.n_tasks);
+            const int task = (int)(id - (unsigned long long)ps * (unsigned long long)a.n_tasks);
+            strip = task % a.n_strips;
+            chunk = task / a.n_strips;
+        } else if (id & SOR_EDGE_QUEUE) {
+            const unsigned long long e = id & ~SOR_EDGE_QUEUE;
+            ps = (int)(e / (unsigned long long)per_edge);
+            const int r = (int)(e - (unsigned long long)ps * (unsigned long long)per_edge);
+            chunk = r >> 1;
+            strip = (r & 1) ? a.n_strips - 1 : 0;
+        } else {
+            ps = (int)(id / (unsigned long long)per_main);
+            const int r = (int)(id - (unsigned long long)ps * (unsigned long long)per_main);
+            chunk = r / (a.n_strips - 2);
+            strip = 1 + r % (a.n_strips - 2);
+        }
         const int it_first = a.it + ps * K;                                        // global number of this pass's first iteration
-        const int strip = task % a.n_strips;
-        int chunk = task / a.n_strips;
         // Slabs are swept from both boundaries inwards (chunks 0, last, 1, last-1, ...): the boundary rows travel to the
         // neighbours while the interior is swept, and every chunk a task of the next pass waits for (its own, the one
         // below, the one above) was claimed a whole pass before it.  (r2 claimed 0, last, 1, 2, ...: chunk `last` of pass
@@ -1097,7 +1151,7 @@ __global__ void __maxnreg__(K == 1 ? 168 : (SOR_RS(K) ? 168 : 255)) sor_persist_
 
         // ---- publish: rows and partials are out
         unsigned long long next_id = 0;
-        if (lane == 0) next_id = atomicAdd(pa.claim, 1ull);      // the next task of this warp, in flight during the fence
+        if (lane == 0) next_id = sor_claim(pa, prefer_edge, total, total_edge);   // the next task of this warp, in flight during the fence
         __threadfence();
         __syncwarp();
         unsigned long long tk = 0;
@@ -1488,7 +1542,23 @@ cudaError_t nsb_launch_sor_persist(nsb_ctx* c, int k, int n_pass, int it0, int c
     // at most two passes are in flight at any time: more warps than that would only poll flags
     const long long useful = (2LL * a.n_tasks + kw - 1) / kw + 1;
     if (blocks > useful) blocks = useful;
-    cudaError_t e = cudaMemsetAsync(c->d_claim, 0, (8 + 2 * (size_t)c->n_chunks) * sizeof(unsigned long long), c->stream);   // claim counter, pass tickets, band tickets
+    // SMs that serve the edge-strip queue first (sor_claim): where the edge strips run bodies of their own -- two iterations
+    // per pass (lane-masked instantiations) and IEEE division (general edge body) --, with a full grid of resident blocks
+    // and enough strips for the split to matter.  How many: the edge strips' share of the work with an edge task costing
+    // w = 2.5 interior ones (it runs ~2.2 x as long even on an SM of its own), plus two -- too few starve every pass
+    // (8192^2, two iterations per pass: 6 SMs 281 us, 10 SMs 192, 13 SMs 173, 16 SMs 176, none 194;
+    //  IEEE division: 8191^2 318 -> 286 us with 13, 6143^2 206 -> 177 with 16, 4100^2 126 -> 100 with 22; profiles/r4b_edge_sms.txt).
+    // NSB_EDGE_SMS=<n> forces a number, 0 switches the split off.
+    pa.edge_sms = 0;
+    {
+        int edge = 0;
+        const char* env = getenv("NSB_EDGE_SMS");
+        if (env) edge = atoi(env);
+        else if (k >= 2 || !c->use_recip) edge = (int)ceil((double)c->sm_count * 5.0 / ((double)(a.n_strips - 2) + 5.0)) + 2;
+        if (edge > c->sm_count / 2) edge = c->sm_count / 2;
+        if (edge > 0 && a.n_strips >= 8 && blocks == (long long)c->sm_count * bps) pa.edge_sms = edge;
+    }
+    cudaError_t e = cudaMemsetAsync(c->d_claim, 0, (8 + 2 * (size_t)c->n_chunks) * sizeof(unsigned long long), c->stream);   // claim counters, pass tickets, band tickets
     if (e != cudaSuccess) return e;
     kern<<<(int)blocks, SOR_KTHREADS(k), SOR_SMEM_BYTES(k), c->stream>>>(pa);
     return NSB_LAUNCHED(c, 1);
